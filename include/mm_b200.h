@@ -1,0 +1,180 @@
+/*
+ * mm_b200.h — C-ABI of the B200-native modality-embedding hot path.
+ *
+ * One shared library (multimeditron_b200/csrc/libmm_b200.so) exports every symbol
+ * declared here.  All pointers are raw DEVICE pointers owned by the caller, all
+ * sizes are element counts unless named *_bytes, `stream` is a cudaStream_t passed
+ * as void*.  No entry point synchronises, allocates, or keeps global mutable state;
+ * every call is re-entrant across streams and devices.  Return value: MM_OK or an
+ * mm_status error (host-detectable argument errors).  Data-dependent errors (an
+ * index out of range, attachment-token count != number of modality rows) are
+ * reported through the caller-supplied device `status` word (see mm_status_bits) so
+ * that the path never forces a host sync; the host wrapper checks it lazily and
+ * raises the same Python exception class the reference raises.
+ *
+ * Each entry point cites the reference interface (relative to /root/reference, or
+ * HF: = transformers 5.5.0) it replaces.
+ */
+#ifndef MM_B200_H_
+#define MM_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum mm_status {
+  MM_OK = 0,
+  MM_ERR_BAD_ARG = 1,        /* shape/alignment/dtype combination not supported            */
+  MM_ERR_CUDA = 2,           /* a CUDA runtime/driver call failed (mm_last_cuda_error())   */
+  MM_ERR_UNSUPPORTED_ARCH = 3/* device is not sm_100                                       */
+} mm_status;
+
+/* bits OR-ed into the device status word by kernels */
+enum mm_status_bits {
+  MM_STATUS_INDEX_OOB = 1,      /* batch_idx/token_range outside [ -size, size )  -> IndexError   */
+  MM_STATUS_COUNT_MISMATCH = 2  /* #attachment tokens != n_rows                  -> RuntimeError */
+};
+
+typedef enum mm_dtype { MM_BF16 = 0, MM_F32 = 1 } mm_dtype;
+
+/* epilogue activation of mm_gemm_bias_act */
+typedef enum mm_act {
+  MM_ACT_NONE = 0,
+  MM_ACT_QUICK_GELU = 1,  /* x*sigmoid(1.702x)   HF:activations.py:117-123 (CLIP MLP)          */
+  MM_ACT_GELU_ERF = 2,    /* exact GELU          src/multimeditron/model/projectors/mlp.py:35,37 */
+  MM_ACT_GELU_TANH = 3    /* gelu_pytorch_tanh   HF:models/siglip (hidden_act)                 */
+} mm_act;
+
+/* Library / build info. */
+const char* mm_version(void);
+int mm_last_cuda_error(void);       /* last cudaError_t seen by this thread (0 = none)         */
+int mm_device_sm_count(int device); /* multiprocessor count, used to size grids                */
+
+/* ------------------------------------------------------------------------------------------
+ * Splice (bit-exact integer/byte work; HBM-bound)
+ * ------------------------------------------------------------------------------------------ */
+
+/*
+ * mm_attach_positions — device prefix-sum of (input_ids == attachment_id).
+ * Replaces the collator-side index build  src/multimeditron/model/data_loader.py:124-141 +
+ * src/multimeditron/model/prompt_tokenizers.py:255-286 : the k-th attachment token in
+ * row-major order of input_ids[B_seq,S] receives row k of the flattened projected stack.
+ *   dest_rows[k]   = flat position (b*S+s) of the k-th attachment token     (int32, capacity n_rows_cap)
+ *   src_of_pos[r]  = k if position r holds the k-th attachment token else -1 (int32, B_seq*S entries; may be NULL)
+ *   count[0]       = total number of attachment tokens                        (int32)
+ *   status        |= MM_STATUS_COUNT_MISMATCH when count != expected_rows (expected_rows >= 0)
+ * workspace: at least mm_attach_positions_workspace_bytes(n_ids) bytes.
+ */
+int64_t mm_attach_positions_workspace_bytes(int64_t n_ids);
+int mm_attach_positions(const int64_t* input_ids, int64_t n_ids, int64_t attachment_id,
+                        int32_t* dest_rows, int64_t n_rows_cap, int32_t* src_of_pos,
+                        int32_t* count, int64_t expected_rows, int32_t* status,
+                        void* workspace, void* stream);
+
+/*
+ * mm_splice_scatter — embedded[dest_rows[k], :] = src[k, :]  (with dtype cast).
+ * Replaces  src/multimeditron/model/model.py:441-444  (ATen index_put_, non-accumulate).
+ * dest is [n_dest_rows, hidden] of dst_dtype, src is [n_rows, hidden] of src_dtype.
+ * Rows with dest_rows[k] < 0 or >= n_dest_rows set MM_STATUS_INDEX_OOB and are skipped.
+ */
+int mm_splice_scatter(void* dest, int64_t n_dest_rows, int64_t hidden, int dst_dtype,
+                      const void* src, int64_t n_rows, int src_dtype,
+                      const int32_t* dest_rows, int32_t* status, void* stream);
+
+/*
+ * mm_splice_scatter_idx — same statement, taking the collator's own int64 index vectors
+ * (processed_multimodal_inputs['batch_idx'/'token_range'], model.py:441-442) and doing the
+ * b*S+t arithmetic (with Python negative-index wrap) on device.
+ */
+int mm_splice_scatter_idx(void* dest, int64_t batch, int64_t seq, int64_t hidden, int dst_dtype,
+                          const void* src, int64_t n_rows, int src_dtype,
+                          const int64_t* batch_idx, const int64_t* token_range,
+                          int32_t* status, void* stream);
+
+/*
+ * mm_embed_splice_fused — one pass that produces inputs_embeds from ids:
+ *   out[r,:] = src_of_pos[r] >= 0 ? src[src_of_pos[r], :] : table[input_ids[r], :]
+ * Replaces  model.py:433 (nn.Embedding lookup) + model.py:441-444 (splice) in one kernel.
+ */
+int mm_embed_splice_fused(void* out, int64_t n_pos, int64_t hidden, int dst_dtype,
+                          const void* table, int64_t vocab,
+                          const int64_t* input_ids, const int32_t* src_of_pos,
+                          const void* src, int64_t n_rows, int src_dtype,
+                          int32_t* status, void* stream);
+
+/* mm_embed_gather — out[r,:] = table[input_ids[r],:]   (model.py:433, ATen embedding). */
+int mm_embed_gather(void* out, int64_t n_pos, int64_t hidden, int dtype, const void* table,
+                    int64_t vocab, const int64_t* input_ids, int32_t* status, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * ViT / projector building blocks (bf16 storage, fp32 accumulate)
+ * ------------------------------------------------------------------------------------------ */
+
+/*
+ * mm_layernorm — y[m,:] = (x[m,:]-mean)*rstd*gamma+beta, fp32 statistics, bf16 in/out.
+ * Replaces nn.LayerNorm call sites HF:models/clip/modeling_clip.py:371,380,677 and
+ * HF:models/siglip/modeling_siglip.py:346,355,617.
+ * Optional row remap: when rows_in_group>0, input row m is read from
+ *   (m / rows_out_group) * rows_in_group + in_row_offset + (m % rows_out_group)
+ * (used to drop the CLS row: image_modality.py:133).
+ */
+int mm_layernorm(const void* x, void* y, const void* gamma, const void* beta, int64_t M,
+                 int64_t D, float eps, int64_t rows_in_group, int64_t rows_out_group,
+                 int64_t in_row_offset, void* stream);
+
+/*
+ * mm_gemm_bias_act — C = act(A · Wᵀ + bias) [+ residual], tcgen05/TMEM GEMM fed by TMA.
+ * Replaces nn.Linear (+activation, + residual add) call sites:
+ *   HF:models/clip/modeling_clip.py:310-312 (q,k,v as one fused N=3D GEMM), :334 (+:377 residual),
+ *   :347-351 (fc1+QuickGELU, fc2 +:382 residual); projectors/mlp.py:33-39.
+ *   A [M,K] bf16 row-major (lda elements), W [N,K] bf16 row-major (nn.Linear.weight layout, ldw),
+ *   bias [N] bf16 or NULL, C [*,N] bf16 (ldc).
+ *   residual (optional, bf16, ldr): row used = (res_mod>0 ? m % res_mod : m) + res_row_off.
+ *     The sum is formed as bf16(bf16(acc+bias) + residual), the reference's rounding points.
+ *   out_row_map (optional, int32[M]): C row written for GEMM row m; <0 = row not stored.
+ *     (drop-CLS image_modality.py:133; splice fusion model.py:441-444)
+ *   Requirements: K % 8 == 0, N % 8 == 0, 16-byte aligned pointers/leading dimensions.
+ */
+int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias,
+                     void* C, int64_t ldc, int64_t M, int64_t N, int64_t K, int act,
+                     const void* residual, int64_t ldr, int64_t res_mod, int64_t res_row_off,
+                     const int32_t* out_row_map, void* stream);
+
+/*
+ * mm_patch_embed — im2col-free implicit GEMM of the patch convolution
+ *   (Conv2d k=s=patch; HF:models/clip/modeling_clip.py:148-154,208-210, siglip :124-130,163-164)
+ * fused with flatten/transpose, +position embedding and the CLS row (modeling_clip.py:210-218).
+ *   pixels [B,3,img,img] fp32 or bf16 (cast to bf16 like :208-209),
+ *   weight [D, ldw] bf16 = conv weight flattened to [D, 3*patch*patch] and zero-padded (once, at load
+ *   time) to ldw >= round_up(3*patch*patch, 64) so that rows are 16-byte aligned for TMA,
+ *   conv_bias [D] bf16 or NULL, pos_emb [T,D] bf16, cls [D] bf16 or NULL (NULL => no CLS row, T=P),
+ *   out [B,T,D] bf16: out[b,0]=cls+pos[0]; out[b,cls_rows+p]=conv(patch p)+bias+pos[cls_rows+p].
+ */
+int mm_patch_embed(const void* pixels, int pixel_dtype, int64_t B, int64_t img, int64_t patch,
+                   const void* weight, int64_t ldw, const void* conv_bias, const void* pos_emb,
+                   const void* cls, void* out, int64_t D, void* stream);
+
+/*
+ * mm_attention_fwd — non-causal softmax(Q·Kᵀ·scale)·V for every (image, head), no mask,
+ * tcgen05 QKᵀ / PV with TMEM accumulators and an online softmax in registers.
+ * Replaces HF:models/clip/modeling_clip.py:318-331 (SDPA, HF:integrations/sdpa_attention.py:40).
+ *   qkv [B*T, 3*D] bf16, columns [q | k | v], head h occupies columns h*head_dim.. of each third;
+ *   out [B*T, D] bf16.  head_dim must be 64.
+ */
+int mm_attention_fwd(const void* qkv, void* out, int64_t B, int64_t T, int64_t heads,
+                     int64_t head_dim, float scale, void* stream);
+
+/*
+ * mm_weighted_expert_sum — out[b,p,:] = sum_e w[b, perm[e]] * x[e,b,p,:]
+ * (MoE 'weighted_average' fusion: image_modality_moe.py:171-177, image_modality_moe_pep.py:212-216
+ *  where perm is the identity).  x [E,B*P,D] bf16, w [B,E] fp32, out [B*P,D] bf16.
+ */
+int mm_weighted_expert_sum(const void* x, const float* w, const int32_t* perm, void* out,
+                           int64_t E, int64_t B, int64_t P, int64_t D, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MM_B200_H_ */
