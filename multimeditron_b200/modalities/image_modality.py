@@ -1,0 +1,148 @@
+"""B200-native image modality — drop-in for `ImageModality` (src/multimeditron/model/modalities/image_modality.py).
+
+model_type "meditron_clip_b200": same config fields (hidden_size, clip_name, projection_type, use_2d_position_ids),
+same processor contract, same state-dict keys (feature_extractor.vision_model.*, projector.projection.{0,2,4}.*),
+same `forward(list[Tensor[3,h,w]]) -> Tensor[B, P, hidden]` — but the ViT forward, the projector and (optionally) the
+splice run on the hand-written sm_100a kernels (multimeditron_b200.vit.TowerRunner).  Inference/frozen-embedder
+path only in this round (the reference's ALIGNMENT/FULL backward is SURVEY.md §8(f)#2).
+"""
+from __future__ import annotations
+
+from typing import Any, Dict, List, Optional
+
+import torch
+
+from ..configs import TOWERS, TowerConfig
+from ..vit import ProjectorWeights, TowerRunner, TowerWeights
+from .base import AutoModality, BaseModality, BaseModalityConfig, BaseModalityProcessor
+from .constants import MODALITY_VALUE_KEY, NUM_EMBEDDINGS_KEY, POSITION_IDS_KEY
+
+
+def resolve_tower(clip_name) -> TowerConfig:
+    """clip_name: a key of configs.TOWERS, a TowerConfig, a dict of its fields, or a local HF checkpoint dir."""
+    if isinstance(clip_name, TowerConfig):
+        return clip_name
+    if isinstance(clip_name, dict):
+        return TowerConfig(**clip_name)
+    if clip_name in TOWERS:
+        return TOWERS[clip_name]
+    from transformers import AutoConfig  # local dir / hub name, like image_modality.py:76
+    vc = AutoConfig.from_pretrained(clip_name).vision_config
+    kind = "siglip" if "siglip" in type(vc).__name__.lower() else "clip"
+    return TowerConfig(kind, vc.image_size, vc.patch_size, vc.hidden_size, vc.intermediate_size,
+                       vc.num_hidden_layers, vc.num_attention_heads, vc.layer_norm_eps, vc.hidden_act)
+
+
+class B200ImageConfig(BaseModalityConfig):
+    def __init__(self, hidden_size: int = 4096, clip_name="openai/clip-vit-large-patch14",
+                 projection_type: str = "mlp", use_2d_position_ids: bool = False, **kwargs):
+        super().__init__(modality_type="image", hidden_size=hidden_size, **kwargs)
+        self.clip_name = clip_name
+        self.projection_type = projection_type
+        self.use_2d_position_ids = use_2d_position_ids
+
+
+class B200ImageProcessor(BaseModalityProcessor):
+    """Same outputs as ImageProcessor.process (image_modality.py:83-110).  PIL images go through the HF image
+    processor saved next to the checkpoint; tensors that are already [3,h,w] pixel values pass through."""
+
+    def __init__(self, config):
+        super().__init__(config)
+        assert config.clip_name is not None, "clip_name must be specified in the config"
+        self.tower = resolve_tower(config.clip_name)
+        self._image_size = self.tower.grid
+        self._num_patches_per_entry = self.tower.num_patches
+        self.image_processor = None
+        if isinstance(config.clip_name, str) and config.clip_name not in TOWERS:
+            from transformers import AutoImageProcessor
+            self.image_processor = AutoImageProcessor.from_pretrained(config.clip_name)
+
+    def process(self, modality: Dict[str, Any]) -> Dict[str, Any]:
+        out = modality.copy()
+        image = modality[MODALITY_VALUE_KEY]
+        if torch.is_tensor(image):
+            out[MODALITY_VALUE_KEY] = image
+        else:
+            if self.image_processor is None:
+                raise ValueError("PIL input needs a checkpoint directory with an image processor (clip_name)")
+            out[MODALITY_VALUE_KEY] = self.image_processor(images=image, return_tensors="pt")["pixel_values"][0]
+        out[NUM_EMBEDDINGS_KEY] = self._num_patches_per_entry
+        if self.config.use_2d_position_ids:
+            g = self._image_size
+            out[POSITION_IDS_KEY] = torch.stack(
+                torch.meshgrid(torch.arange(g, dtype=torch.long), torch.arange(g, dtype=torch.long), indexing="ij"),
+                dim=-1).reshape(self._num_patches_per_entry, 2)
+        return out
+
+
+@AutoModality.register("meditron_clip_b200")
+class B200ImageModality(BaseModality):
+    config_class = B200ImageConfig
+    preprocessor_class = B200ImageProcessor
+
+    def __init__(self, config: B200ImageConfig, state_dict: Optional[dict] = None, device=None):
+        super().__init__(config)
+        self.vision_tower_name = config.clip_name
+        assert self.vision_tower_name is not None, "vision_tower_name must be specified in the config"
+        self.tower = resolve_tower(config.clip_name)
+        self.embedding_size = self.tower.hidden_size
+        self._num_patches_per_entry = self.tower.num_patches
+        self._runner: Optional[TowerRunner] = None
+        self._frozen = True
+        if state_dict is not None:
+            self.load_reference_state_dict(state_dict, device or torch.device("cuda", torch.cuda.current_device()))
+
+    # -- weights ------------------------------------------------------------------------------------------------
+    def load_reference_state_dict(self, sd: dict, device) -> "B200ImageModality":
+        """`sd` uses the reference's keys (ImageModality.state_dict())."""
+        self._runner = TowerRunner(TowerWeights(self.tower, sd, device))
+        return self
+
+    @classmethod
+    def from_reference(cls, ref_modality, device) -> "B200ImageModality":
+        """Build from an instantiated reference `ImageModality` (same config, same parameters)."""
+        c = ref_modality.config
+        vc = ref_modality.feature_extractor.vision_model.config
+        tower = TowerConfig("clip", vc.image_size, vc.patch_size, vc.hidden_size, vc.intermediate_size,
+                            vc.num_hidden_layers, vc.num_attention_heads, vc.layer_norm_eps, vc.hidden_act)
+        cfg = B200ImageConfig(hidden_size=c.hidden_size, clip_name=tower, projection_type=c.projection_type,
+                              use_2d_position_ids=c.use_2d_position_ids)
+        return cls(cfg, state_dict=ref_modality.state_dict(), device=device)
+
+    @property
+    def runner(self) -> TowerRunner:
+        if self._runner is None:
+            raise RuntimeError("B200ImageModality has no weights loaded (call load_reference_state_dict)")
+        return self._runner
+
+    # -- the plugin call ----------------------------------------------------------------------------------------
+    def _stack(self, inputs) -> torch.Tensor:
+        dev = self.runner.w.device
+        if torch.is_tensor(inputs):
+            return inputs.to(dev, non_blocking=True)
+        inputs = list(inputs)
+        if len(inputs) and inputs[0].is_cuda:
+            return torch.stack(inputs, dim=0)
+        # one pinned staging buffer + one async H2D instead of the reference's pageable, synchronous copy (:131-132)
+        stacked = torch.stack(inputs, dim=0)
+        return stacked.pin_memory().to(dev, non_blocking=True) if stacked.numel() else stacked.to(dev)
+
+    @torch.no_grad()
+    def forward(self, inputs: List[torch.Tensor]) -> torch.Tensor:
+        return self.runner.forward(self._stack(inputs))
+
+    @torch.no_grad()
+    def forward_into(self, inputs, embedded_tokens: torch.Tensor, dest_rows: torch.Tensor) -> torch.Tensor:
+        """forward + splice in one go: projected row k lands in embedded_tokens.view(-1,H)[dest_rows[k]]."""
+        r = self.runner
+        return r.project(r.features(self._stack(inputs)), out=embedded_tokens, out_row_map=dest_rows)
+
+    # -- training-mode switches (interface parity; backward is not part of this round) ------------------------------
+    def freeze_modality_embedder(self):
+        self._frozen = True
+
+    def unfreeze_modality_embedder(self):
+        raise NotImplementedError("ViT backward on the B200 path is SURVEY.md §8(f)#2 (next)")
+
+    def unfreeze_projection(self):
+        raise NotImplementedError("projector backward on the B200 path is SURVEY.md §8(f)#2 (next)")

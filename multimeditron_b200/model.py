@@ -1,0 +1,103 @@
+"""Model-level entry of the hot path: `embed_modalities_with_text` on the B200 kernels.
+
+Mirror of the part of `MultiModalModelForCausalLM` that is on the path (src/multimeditron/model/model.py):
+  * processors()                      :379-380
+  * _get_modality_by_name             :382-396   (KeyError / TypeError behaviour)
+  * embed_modalities_with_text        :410-446   (embedding lookup + modality forward + splice)
+The LLM itself (HF AutoModelForCausalLM) is out of scope: only its embedding table is touched by the path, so the
+embedder takes that table.  `forward(...)` returns inputs_embeds, which the caller passes to its LLM as
+`inputs_embeds=` exactly like model.py:517-526 does.
+"""
+from __future__ import annotations
+
+from typing import Any, Dict, List, Optional
+
+import torch
+
+from . import ops
+from .modalities.base import BaseModality, BaseModalityProcessor
+
+
+class B200MultiModalEmbedder(torch.nn.Module):
+    def __init__(self, embed_table: torch.Tensor, modalities: List[BaseModality], attachment_token_idx: int,
+                 processors: Optional[Dict[str, BaseModalityProcessor]] = None, fuse_splice: bool = True):
+        super().__init__()
+        self.embed_table = embed_table  # [V, H] on the GPU, LLM dtype
+        self.attachment_token_idx = int(attachment_token_idx)
+        self.fuse_splice = fuse_splice
+        self.modalities_by_type: Dict[str, BaseModality] = {}
+        self.processors_by_type: Dict[str, BaseModalityProcessor] = dict(processors or {})
+        for m in modalities:
+            t = m.config.modality_type
+            if t in self.modalities_by_type:  # model.py:275-278
+                raise ValueError(f"Modality type {t} has already been registered")
+            self.modalities_by_type[t] = m
+        self.modalities_with_projection = torch.nn.ModuleList(modalities)
+        self._status = None
+
+    # model.py:379-380
+    def processors(self) -> Dict[str, BaseModalityProcessor]:
+        return self.processors_by_type
+
+    # model.py:382-396
+    def _get_modality_by_name(self, name: str) -> BaseModality:
+        if name not in self.modalities_by_type:
+            raise KeyError(f"Modality {name} not found in registered modalities")
+        m = self.modalities_by_type[name]
+        if not isinstance(m, BaseModality):
+            raise TypeError(f"Registered modality {name} is not a BaseModality")
+        return m
+
+    def status(self) -> torch.Tensor:
+        if self._status is None or self._status.device != self.embed_table.device:
+            self._status = ops.new_status(self.embed_table.device)
+        return self._status
+
+    def check(self):
+        """Lazy (one sync) check of data-dependent errors; raises IndexError / RuntimeError like the reference."""
+        if self._status is not None:
+            ops.raise_for_status(self._status)
+            self._status.zero_()
+
+    @torch.no_grad()
+    def embed_modalities_with_text(self, input_ids: torch.Tensor, processed_multimodal_inputs: Dict[str, Any],
+                                   positions_from: str = "collator") -> torch.Tensor:
+        """model.py:410-446.  positions_from:
+          'collator' — use processed_multimodal_inputs['batch_idx'/'token_range'] as the reference does;
+          'device'   — ignore them and derive the positions from input_ids with the device prefix sum
+                       (valid for a single modality type); no index H2D at all."""
+        dev = self.embed_table.device
+        ids = input_ids.to(dev, non_blocking=True)
+        st = self.status()
+        stacks = processed_multimodal_inputs["stacked"]
+        B, S = ids.shape
+        H = self.embed_table.shape[1]
+        if positions_from == "device" and len(stacks) > 1:
+            raise ValueError("device-side positions need a single modality type")
+        embedded = ops.embed_gather(self.embed_table, ids, status=st)                       # :433
+        for name, stack in stacks.items():
+            modality = self._get_modality_by_name(name)
+            if positions_from == "device":
+                n_rows = len(stack) * modality._num_patches_per_entry
+                dest_rows, _, _ = ops.attach_positions(ids, self.attachment_token_idx, expected_rows=n_rows,
+                                                       want_src_of_pos=False, status=st)
+            else:
+                bi = processed_multimodal_inputs["batch_idx"][name].to(dev, non_blocking=True)
+                tr = processed_multimodal_inputs["token_range"][name].to(dev, non_blocking=True)
+                dest_rows = None
+            fused = (self.fuse_splice and hasattr(modality, "forward_into") and embedded.dtype == torch.bfloat16)
+            if fused and dest_rows is not None:
+                modality.forward_into(stack, embedded, dest_rows)                         # :439 + :441-444 fused
+                continue
+            proj = modality(stack)                                                        # :439
+            proj2d = proj.reshape(-1, proj.shape[-1])
+            if dest_rows is not None:
+                if proj2d.shape[0] != dest_rows.numel():
+                    raise RuntimeError("shape mismatch: number of modality embeddings != attachment positions")
+                ops.splice_scatter(embedded.view(B * S, H), proj2d.contiguous(), dest_rows, status=st)
+            else:
+                ops.splice_scatter_idx(embedded, proj2d.contiguous(), bi, tr, status=st)  # :441-444
+        return embedded
+
+    def forward(self, input_ids: torch.Tensor, processed_multimodal_inputs: Dict[str, Any], **kw) -> torch.Tensor:
+        return self.embed_modalities_with_text(input_ids, processed_multimodal_inputs, **kw)

@@ -1,0 +1,233 @@
+"""torch.Tensor-level wrappers over the C-ABI (include/mm_b200.h).
+
+PyTorch is plumbing here: it owns device memory and the CUDA stream; every op hands raw pointers
+to the hand-written sm_100a kernels.  There is no fallback: a non-CUDA tensor raises.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+
+MM_BF16, MM_F32 = 0, 1
+ACT_NONE, ACT_QUICK_GELU, ACT_GELU_ERF, ACT_GELU_TANH = 0, 1, 2, 3
+ACT_BY_NAME = {
+    None: ACT_NONE, "none": ACT_NONE, "quick_gelu": ACT_QUICK_GELU, "gelu": ACT_GELU_ERF,
+    "gelu_pytorch_tanh": ACT_GELU_TANH, "gelu_tanh": ACT_GELU_TANH,
+}
+STATUS_INDEX_OOB, STATUS_COUNT_MISMATCH = 1, 2
+
+
+class MMError(RuntimeError):
+    pass
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.bfloat16:
+        return MM_BF16
+    if t.dtype == torch.float32:
+        return MM_F32
+    raise TypeError(f"unsupported dtype {t.dtype} (bf16 / fp32 only)")
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise MMError("multimeditron_b200 ops need CUDA tensors (sm_100a kernels only, no CPU fallback)")
+
+
+def _check(rc: int, what: str):
+    if rc != 0:
+        lib = _lib.load()
+        names = {1: "MM_ERR_BAD_ARG", 2: "MM_ERR_CUDA", 3: "MM_ERR_UNSUPPORTED_ARCH"}
+        raise MMError(f"{what} failed: {names.get(rc, rc)} (cuda error {lib.mm_last_cuda_error()})")
+
+
+def new_status(device) -> torch.Tensor:
+    return torch.zeros(1, dtype=torch.int32, device=device)
+
+
+def raise_for_status(status: torch.Tensor):
+    """Lazy check of the device status word (one D2H sync). Raises what the reference raises."""
+    s = int(status.item())
+    if s & STATUS_INDEX_OOB:
+        raise IndexError("index out of range in splice (batch_idx/token_range/input_ids)")
+    if s & STATUS_COUNT_MISMATCH:
+        # model.py:441 -> index_put_ shape mismatch is a RuntimeError in the reference
+        raise RuntimeError("shape mismatch: number of attachment tokens != number of modality embeddings")
+
+
+# ------------------------------------------------------------------------------------------ splice
+def attach_positions(input_ids: torch.Tensor, attachment_id: int, expected_rows: int = -1,
+                     want_src_of_pos: bool = True, status: torch.Tensor | None = None):
+    """-> (dest_rows int32[cap], src_of_pos int32[n_ids] | None, count int32[1]) without host sync."""
+    _cuda(input_ids)
+    lib = _lib.load()
+    ids = input_ids.contiguous().view(-1)
+    assert ids.dtype == torch.int64
+    n = ids.numel()
+    cap = expected_rows if expected_rows >= 0 else n
+    dev = ids.device
+    dest_rows = torch.empty(max(cap, 1), dtype=torch.int32, device=dev)
+    sop = torch.empty(max(n, 1), dtype=torch.int32, device=dev) if want_src_of_pos else None
+    count = torch.empty(1, dtype=torch.int32, device=dev)
+    ws = torch.empty(lib.mm_attach_positions_workspace_bytes(n), dtype=torch.uint8, device=dev)
+    rc = lib.mm_attach_positions(_ptr(ids), n, int(attachment_id), _ptr(dest_rows), cap, _ptr(sop), _ptr(count),
+                                 int(expected_rows), _ptr(status), _ptr(ws), _stream())
+    _check(rc, "mm_attach_positions")
+    return dest_rows[:cap], (sop[:n] if sop is not None else None), count
+
+
+def splice_scatter(dest: torch.Tensor, src: torch.Tensor, dest_rows: torch.Tensor,
+                   status: torch.Tensor | None = None) -> torch.Tensor:
+    """dest.view(-1,H)[dest_rows[k]] = src.view(-1,H)[k]   (in place; model.py:441-444)."""
+    _cuda(dest, src, dest_rows)
+    lib = _lib.load()
+    H = dest.shape[-1]
+    assert dest.is_contiguous() and src.is_contiguous() and src.shape[-1] == H
+    assert dest_rows.dtype == torch.int32 and dest_rows.is_contiguous()
+    n_rows = src.numel() // H if H else 0
+    assert dest_rows.numel() >= n_rows
+    rc = lib.mm_splice_scatter(_ptr(dest), dest.numel() // H if H else 0, H, _dt(dest), _ptr(src), n_rows, _dt(src),
+                               _ptr(dest_rows), _ptr(status), _stream())
+    _check(rc, "mm_splice_scatter")
+    return dest
+
+
+def splice_scatter_idx(dest: torch.Tensor, src: torch.Tensor, batch_idx: torch.Tensor, token_range: torch.Tensor,
+                       status: torch.Tensor | None = None) -> torch.Tensor:
+    """dest[batch_idx, token_range] = src.view(-1,H)  with the collator's int64 index vectors."""
+    _cuda(dest, src, batch_idx, token_range)
+    lib = _lib.load()
+    assert dest.dim() == 3 and dest.is_contiguous() and src.is_contiguous()
+    B, S, H = dest.shape
+    n_rows = src.numel() // H if H else 0
+    if batch_idx.numel() != token_range.numel() or batch_idx.numel() != n_rows:
+        # same class/condition as index_put_ in the reference (host-known sizes -> no device round trip)
+        raise RuntimeError(
+            f"shape mismatch: value tensor of shape [{n_rows}, {H}] cannot be broadcast to indexing result of "
+            f"shape [{batch_idx.numel()}, {H}]")
+    bi = batch_idx.contiguous().to(torch.int64)
+    tr = token_range.contiguous().to(torch.int64)
+    rc = lib.mm_splice_scatter_idx(_ptr(dest), B, S, H, _dt(dest), _ptr(src), n_rows, _dt(src), _ptr(bi), _ptr(tr),
+                                   _ptr(status), _stream())
+    _check(rc, "mm_splice_scatter_idx")
+    return dest
+
+
+def embed_gather(table: torch.Tensor, input_ids: torch.Tensor, status: torch.Tensor | None = None) -> torch.Tensor:
+    _cuda(table, input_ids)
+    lib = _lib.load()
+    V, H = table.shape
+    ids = input_ids.contiguous()
+    out = torch.empty(*ids.shape, H, dtype=table.dtype, device=table.device)
+    rc = lib.mm_embed_gather(_ptr(out), ids.numel(), H, _dt(table), _ptr(table.contiguous()), V, _ptr(ids),
+                             _ptr(status), _stream())
+    _check(rc, "mm_embed_gather")
+    return out
+
+
+def embed_splice_fused(table: torch.Tensor, input_ids: torch.Tensor, src_of_pos: torch.Tensor, src: torch.Tensor,
+                       status: torch.Tensor | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
+    _cuda(table, input_ids, src_of_pos, src)
+    lib = _lib.load()
+    V, H = table.shape
+    ids = input_ids.contiguous()
+    if out is None:
+        out = torch.empty(*ids.shape, H, dtype=table.dtype, device=table.device)
+    n_rows = src.numel() // H if H else 0
+    rc = lib.mm_embed_splice_fused(_ptr(out), ids.numel(), H, _dt(out), _ptr(table.contiguous()), V, _ptr(ids),
+                                   _ptr(src_of_pos), _ptr(src.contiguous()), n_rows, _dt(src), _ptr(status),
+                                   _stream())
+    _check(rc, "mm_embed_splice_fused")
+    return out
+
+
+# ------------------------------------------------------------------------------------------ ViT blocks
+def layernorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float, out: torch.Tensor | None = None,
+              rows_in_group: int = 0, rows_out_group: int = 0, in_row_offset: int = 0) -> torch.Tensor:
+    _cuda(x, gamma, beta)
+    lib = _lib.load()
+    D = x.shape[-1]
+    assert x.dtype == torch.bfloat16 and x.is_contiguous()
+    if out is None:
+        out = torch.empty_like(x)
+    M = out.numel() // D
+    rc = lib.mm_layernorm(_ptr(x), _ptr(out), _ptr(gamma), _ptr(beta), M, D, float(eps), rows_in_group,
+                          rows_out_group, in_row_offset, _stream())
+    _check(rc, "mm_layernorm")
+    return out
+
+
+def gemm_bias_act(a: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None, act: int = ACT_NONE,
+                  residual: torch.Tensor | None = None, res_mod: int = 0, res_row_off: int = 0,
+                  out: torch.Tensor | None = None, out_row_map: torch.Tensor | None = None) -> torch.Tensor:
+    """out = act(a @ w.T + bias) [+ residual]; a [M,K], w [N,K] bf16 (row strides may exceed K)."""
+    _cuda(a, w, bias, residual, out, out_row_map)
+    lib = _lib.load()
+    assert a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and a.dim() == 2 and w.dim() == 2
+    assert a.stride(1) == 1 and w.stride(1) == 1
+    M, K = a.shape
+    N = w.shape[0]
+    assert w.shape[1] == K
+    if out is None:
+        assert out_row_map is None
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=a.device)
+    assert out.dtype == torch.bfloat16 and out.stride(-1) == 1
+    ldc = out.stride(-2) if out.dim() >= 2 else N
+    ldr = residual.stride(-2) if residual is not None else 0
+    rc = lib.mm_gemm_bias_act(_ptr(a), a.stride(0), _ptr(w), w.stride(0), _ptr(bias), _ptr(out), ldc, M, N, K,
+                              int(act), _ptr(residual), ldr, int(res_mod), int(res_row_off), _ptr(out_row_map),
+                              _stream())
+    _check(rc, "mm_gemm_bias_act")
+    return out
+
+
+def patch_embed(pixels: torch.Tensor, weight_padded: torch.Tensor, conv_bias, pos_emb: torch.Tensor, cls,
+                patch: int, out: torch.Tensor | None = None) -> torch.Tensor:
+    """pixels [B,3,img,img] fp32/bf16; weight_padded [D, Kpad] bf16 (zero padded) -> [B,T,D] bf16."""
+    _cuda(pixels, weight_padded, conv_bias, pos_emb, cls)
+    lib = _lib.load()
+    B, Cc, img, img2 = pixels.shape
+    assert Cc == 3 and img == img2 and pixels.is_contiguous()
+    D = weight_padded.shape[0]
+    T = pos_emb.shape[0]
+    if out is None:
+        out = torch.empty(B, T, D, dtype=torch.bfloat16, device=pixels.device)
+    rc = lib.mm_patch_embed(_ptr(pixels), _dt(pixels), B, img, patch, _ptr(weight_padded), weight_padded.stride(0),
+                            _ptr(conv_bias), _ptr(pos_emb), _ptr(cls), _ptr(out), D, _stream())
+    _check(rc, "mm_patch_embed")
+    return out
+
+
+def attention_fwd(qkv: torch.Tensor, B: int, T: int, heads: int, head_dim: int, scale: float,
+                  out: torch.Tensor | None = None) -> torch.Tensor:
+    _cuda(qkv)
+    lib = _lib.load()
+    D = heads * head_dim
+    assert qkv.dtype == torch.bfloat16 and qkv.is_contiguous() and qkv.numel() == B * T * 3 * D
+    if out is None:
+        out = torch.empty(B * T, D, dtype=torch.bfloat16, device=qkv.device)
+    rc = lib.mm_attention_fwd(_ptr(qkv), _ptr(out), B, T, heads, head_dim, float(scale), _stream())
+    _check(rc, "mm_attention_fwd")
+    return out
+
+
+def weighted_expert_sum(x: torch.Tensor, w: torch.Tensor, perm: torch.Tensor | None, B: int, P: int) -> torch.Tensor:
+    """x [E, B*P, D] bf16, w [B,E] fp32, perm int32[E] | None -> [B*P, D] bf16."""
+    _cuda(x, w, perm)
+    lib = _lib.load()
+    E, R, D = x.shape
+    assert R == B * P and x.is_contiguous() and w.dtype == torch.float32 and w.is_contiguous()
+    out = torch.empty(R, D, dtype=torch.bfloat16, device=x.device)
+    rc = lib.mm_weighted_expert_sum(_ptr(x), _ptr(w), _ptr(perm), _ptr(out), E, B, P, D, _stream())
+    _check(rc, "mm_weighted_expert_sum")
+    return out

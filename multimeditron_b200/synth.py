@@ -1,0 +1,110 @@
+"""Deterministic synthetic weights / inputs with the reference's state-dict key names.
+
+There is no network for checkpoints, so tests and bench.py use random-init towers.  Per SURVEY.md
+§8 C4 the reference's own random init leaves every bias 0 and LayerNorm at (1, 0), which would never
+exercise the fused bias/LN paths, so biases ~ N(0,0.02), gamma ~ 1+N(0,0.1), beta ~ N(0,0.1).
+Values are drawn on the CPU generator in a fixed key order, so a (config, seed) pair names the same
+tensors on every machine with this torch build.
+"""
+from __future__ import annotations
+
+import torch
+
+from .configs import TowerConfig
+
+VM = "feature_extractor.vision_model."
+
+
+def tower_keys(cfg: TowerConfig):
+    """(key, shape, kind) in canonical order; kind in {w, b, g(amma), beta}."""
+    D, I, p = cfg.hidden_size, cfg.intermediate_size, cfg.patch_size
+    out = []
+    if cfg.has_cls:
+        out.append((VM + "embeddings.class_embedding", (D,), "w"))
+    out.append((VM + "embeddings.patch_embedding.weight", (D, 3, p, p), "w"))
+    if cfg.conv_bias:
+        out.append((VM + "embeddings.patch_embedding.bias", (D,), "b"))
+    out.append((VM + "embeddings.position_embedding.weight", (cfg.num_tokens, D), "w"))
+    if cfg.kind == "clip":
+        out += [(VM + "pre_layrnorm.weight", (D,), "g"), (VM + "pre_layrnorm.bias", (D,), "beta")]
+    for i in range(cfg.num_hidden_layers):
+        L = f"{VM}encoder.layers.{i}."
+        out += [(L + "layer_norm1.weight", (D,), "g"), (L + "layer_norm1.bias", (D,), "beta")]
+        for n in ("q_proj", "k_proj", "v_proj", "out_proj"):
+            out += [(L + f"self_attn.{n}.weight", (D, D), "w"), (L + f"self_attn.{n}.bias", (D,), "b")]
+        out += [(L + "layer_norm2.weight", (D,), "g"), (L + "layer_norm2.bias", (D,), "beta")]
+        out += [(L + "mlp.fc1.weight", (I, D), "w"), (L + "mlp.fc1.bias", (I,), "b")]
+        out += [(L + "mlp.fc2.weight", (D, I), "w"), (L + "mlp.fc2.bias", (D,), "b")]
+    out += [(VM + "post_layernorm.weight", (D,), "g"), (VM + "post_layernorm.bias", (D,), "beta")]
+    return out
+
+
+def projector_keys(D: int, H: int, prefix: str = "projector."):
+    """MLPProjector: projection.{0,2,4} (src/multimeditron/model/projectors/mlp.py:33-39)."""
+    return [
+        (prefix + "projection.0.weight", (D, D), "w"), (prefix + "projection.0.bias", (D,), "b"),
+        (prefix + "projection.2.weight", (H, D), "w"), (prefix + "projection.2.bias", (H,), "b"),
+        (prefix + "projection.4.weight", (H, H), "w"), (prefix + "projection.4.bias", (H,), "b"),
+    ]
+
+
+def _draw(keys, gen, dtype, device):
+    sd = {}
+    for k, shape, kind in keys:
+        t = torch.randn(shape, generator=gen, dtype=torch.float32)
+        if kind in ("w", "b"):
+            t = t * 0.02
+        elif kind == "g":
+            t = 1.0 + 0.1 * t
+        else:
+            t = 0.1 * t
+        sd[k] = t.to(dtype).to(device)
+    return sd
+
+
+def make_modality_state_dict(cfg: TowerConfig, llm_hidden: int, seed: int = 0, dtype=torch.float32, device="cpu"):
+    """State dict of one `meditron_clip`-style modality: feature_extractor.vision_model.* + projector.*"""
+    gen = torch.Generator().manual_seed(seed)
+    return _draw(tower_keys(cfg) + projector_keys(cfg.hidden_size, llm_hidden), gen, dtype, device)
+
+
+def make_pixels(cfg: TowerConfig, batch: int, seed: int = 0, device="cpu"):
+    """Post-normalisation CLIP pixels are ~N(0,1); fp32 like the processor output."""
+    gen = torch.Generator().manual_seed(1000 + seed)
+    return torch.randn(batch, 3, cfg.image_size, cfg.image_size, generator=gen, dtype=torch.float32).to(device)
+
+
+def make_sequences(batch: int, seq_len: int, images_per_row: int, tokens_per_image: int, vocab: int, attach_id: int,
+                   start_id: int, end_id: int, pad_id: int, seed: int = 0, padding_side: str = "right",
+                   min_len: int | None = None):
+    """input_ids [batch, seq_len] int64 in the reference's expanded form
+    (<image_start> + N x attachment + <image_end> per image, prompt_tokenizers.py:288-306), images at seeded
+    sorted offsets, remaining ids uniform in [0, vocab) excluding the special ids, ragged rows padded."""
+    gen = torch.Generator().manual_seed(2000 + seed)
+    special = {attach_id, start_id, end_id, pad_id}
+    block = tokens_per_image + 2
+    ids = torch.full((batch, seq_len), pad_id, dtype=torch.int64)
+    mask = torch.zeros((batch, seq_len), dtype=torch.bool)
+    for b in range(batch):
+        lo = max(min_len if min_len is not None else seq_len, images_per_row * block)
+        length = int(torch.randint(lo, seq_len + 1, (1,), generator=gen)) if lo < seq_len else seq_len
+        n_text = length - images_per_row * block
+        assert n_text >= 0, "sequence too short for the requested images"
+        text = torch.randint(0, vocab, (n_text,), generator=gen)
+        for s in special:  # remap collisions deterministically
+            text[text == s] = (s + 7) % vocab if (s + 7) % vocab not in special else 0
+        cuts = torch.sort(torch.randint(0, n_text + 1, (images_per_row,), generator=gen)).values.tolist()
+        row, prev = [], 0
+        img = torch.tensor([start_id] + [attach_id] * tokens_per_image + [end_id], dtype=torch.int64)
+        for c in cuts:
+            row += [text[prev:c], img]
+            prev = c
+        row.append(text[prev:])
+        row = torch.cat(row)
+        if padding_side == "right":
+            ids[b, :length] = row
+            mask[b, :length] = True
+        else:
+            ids[b, seq_len - length:] = row
+            mask[b, seq_len - length:] = True
+    return ids, mask

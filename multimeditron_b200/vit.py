@@ -1,0 +1,157 @@
+"""Host-side driver of the image tower + projector on the sm_100a kernels.
+
+`TowerWeights` packs a reference state dict (feature_extractor.vision_model.* / projector.projection.{0,2,4}.*)
+once into the layouts the kernels want (fused [3D,D] QKV weight, zero-padded [D,Kpad] patch weight, bf16).
+`TowerRunner.forward` issues, per encoder layer, 7 kernel launches on the current stream:
+    LN1 -> GEMM(qkv,+bias) -> attention -> GEMM(out,+bias,+residual) -> LN2 -> GEMM(fc1,+bias,act) ->
+    GEMM(fc2,+bias,+residual)
+then the 3 projector GEMMs (bias+erf-GELU epilogues); the last one can scatter its rows straight into
+inputs_embeds (splice fused into the epilogue).  No host sync anywhere on the path.
+
+Reference: image_modality.py:130-137; HF:models/clip/modeling_clip.py:667-692; projectors/mlp.py:33-39.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+from .configs import TowerConfig
+
+VM = "feature_extractor.vision_model."
+
+
+def _bf(t: torch.Tensor, device) -> torch.Tensor:
+    return t.detach().to(device=device, dtype=torch.bfloat16).contiguous()
+
+
+class TowerWeights:
+    """Device-resident, kernel-ready copy of one modality's parameters (replicated per GPU)."""
+
+    def __init__(self, cfg: TowerConfig, sd: dict, device, vm_prefix: str = VM, with_projector: bool = True,
+                 proj_prefix: str = "projector."):
+        self.cfg = cfg
+        self.device = torch.device(device)
+        D = cfg.hidden_size
+        dev = self.device
+        w = sd[vm_prefix + "embeddings.patch_embedding.weight"].reshape(D, -1)
+        kpad = (cfg.patch_k + 63) // 64 * 64
+        wp = torch.zeros(D, kpad, dtype=torch.bfloat16, device=dev)
+        wp[:, : cfg.patch_k] = _bf(w, dev)
+        self.patch_w = wp
+        self.patch_b = _bf(sd[vm_prefix + "embeddings.patch_embedding.bias"], dev) if cfg.conv_bias else None
+        self.pos = _bf(sd[vm_prefix + "embeddings.position_embedding.weight"], dev)
+        self.cls = _bf(sd[vm_prefix + "embeddings.class_embedding"], dev) if cfg.has_cls else None
+        if cfg.kind == "clip":
+            self.pre_ln = (_bf(sd[vm_prefix + "pre_layrnorm.weight"], dev), _bf(sd[vm_prefix + "pre_layrnorm.bias"], dev))
+        else:
+            self.pre_ln = None
+            self.post_ln = (_bf(sd[vm_prefix + "post_layernorm.weight"], dev),
+                            _bf(sd[vm_prefix + "post_layernorm.bias"], dev))
+        self.layers = []
+        for i in range(cfg.num_hidden_layers):
+            L = f"{vm_prefix}encoder.layers.{i}."
+            g = lambda n: _bf(sd[L + n], dev)  # noqa: E731
+            self.layers.append(dict(
+                ln1=(g("layer_norm1.weight"), g("layer_norm1.bias")),
+                wqkv=torch.cat([g("self_attn.q_proj.weight"), g("self_attn.k_proj.weight"),
+                                g("self_attn.v_proj.weight")], 0).contiguous(),
+                bqkv=torch.cat([g("self_attn.q_proj.bias"), g("self_attn.k_proj.bias"),
+                                g("self_attn.v_proj.bias")], 0).contiguous(),
+                wo=g("self_attn.out_proj.weight"), bo=g("self_attn.out_proj.bias"),
+                ln2=(g("layer_norm2.weight"), g("layer_norm2.bias")),
+                w1=g("mlp.fc1.weight"), b1=g("mlp.fc1.bias"),
+                w2=g("mlp.fc2.weight"), b2=g("mlp.fc2.bias"),
+            ))
+        self.proj = None
+        if with_projector:
+            self.proj = ProjectorWeights(sd, dev, proj_prefix)
+
+
+class ProjectorWeights:
+    """MLPProjector parameters (projectors/mlp.py:33-39) in bf16 on device."""
+
+    def __init__(self, sd: dict, device, prefix: str = "projector."):
+        p = prefix + "projection."
+        self.w0, self.b0 = _bf(sd[p + "0.weight"], device), _bf(sd[p + "0.bias"], device)
+        self.w2, self.b2 = _bf(sd[p + "2.weight"], device), _bf(sd[p + "2.bias"], device)
+        self.w4, self.b4 = _bf(sd[p + "4.weight"], device), _bf(sd[p + "4.bias"], device)
+        self.hidden = self.w4.shape[0]
+
+
+class TowerRunner:
+    """Runs the tower (and projector) for batches of images; activation workspaces are cached per batch size."""
+
+    def __init__(self, weights: TowerWeights):
+        self.w = weights
+        self.cfg = weights.cfg
+        self._ws = {}
+
+    # -- workspaces ----------------------------------------------------------------------------------------
+    def _workspace(self, B: int):
+        ws = self._ws.get(B)
+        if ws is None:
+            c, dev = self.cfg, self.w.device
+            M, D, I = B * c.num_tokens, c.hidden_size, c.intermediate_size
+            e = lambda *s: torch.empty(*s, dtype=torch.bfloat16, device=dev)  # noqa: E731
+            ws = dict(x=e(M, D), h=e(M, D), qkv=e(M, 3 * D), attn=e(M, D), mlp=e(M, I), feats=e(B * c.num_patches, D))
+            if c.has_cls:  # GEMM row m (token) -> compact feature row, CLS rows dropped (image_modality.py:133)
+                m = torch.arange(M, device=dev, dtype=torch.int64)
+                t = m % c.num_tokens
+                ws["drop_cls"] = torch.where(t == 0, torch.full_like(m, -1),
+                                             (m // c.num_tokens) * c.num_patches + t - 1).to(torch.int32)
+            self._ws = {B: ws}  # keep only the latest batch size resident
+        return ws
+
+    # -- tower -----------------------------------------------------------------------------------------------
+    def features(self, pixels: torch.Tensor) -> torch.Tensor:
+        """pixels [B,3,img,img] (fp32 or bf16, CUDA) -> encoder features [B*P, D] bf16 (CLS dropped)."""
+        c, w = self.cfg, self.w
+        if pixels.shape[-1] != c.image_size or pixels.shape[-2] != c.image_size:
+            # same exception class / message as HF:models/clip/modeling_clip.py:204-207
+            raise ValueError(f"Input image size ({pixels.shape[-2]}*{pixels.shape[-1]}) doesn't match model "
+                             f"({c.image_size}*{c.image_size}).")
+        B = pixels.shape[0]
+        ws = self._workspace(B)
+        x, h, qkv, attn, mlp, feats = ws["x"], ws["h"], ws["qkv"], ws["attn"], ws["mlp"], ws["feats"]
+        T, D, nh, hd = c.num_tokens, c.hidden_size, c.num_attention_heads, c.head_dim
+        act = ops.ACT_BY_NAME[c.hidden_act]
+        ops.patch_embed(pixels.contiguous(), w.patch_w, w.patch_b, w.pos, w.cls, c.patch_size, out=x.view(B, T, D))
+        if w.pre_ln is not None:
+            ops.layernorm(x, w.pre_ln[0], w.pre_ln[1], c.layer_norm_eps, out=x)
+        n_layers = len(w.layers)
+        for i, L in enumerate(w.layers):
+            ops.layernorm(x, L["ln1"][0], L["ln1"][1], c.layer_norm_eps, out=h)
+            ops.gemm_bias_act(h, L["wqkv"], L["bqkv"], out=qkv)
+            ops.attention_fwd(qkv, B, T, nh, hd, hd ** -0.5, out=attn)
+            ops.gemm_bias_act(attn, L["wo"], L["bo"], residual=x, out=x)
+            ops.layernorm(x, L["ln2"][0], L["ln2"][1], c.layer_norm_eps, out=h)
+            ops.gemm_bias_act(h, L["w1"], L["b1"], act=act, out=mlp)
+            last = i == n_layers - 1
+            if last and c.has_cls:
+                # last fc2 writes the compact [B*P, D] feature matrix directly (CLS rows never stored)
+                ops.gemm_bias_act(mlp, L["w2"], L["b2"], residual=x, out=feats, out_row_map=ws["drop_cls"])
+            else:
+                ops.gemm_bias_act(mlp, L["w2"], L["b2"], residual=x, out=x)
+        if not c.has_cls:
+            ops.layernorm(x, w.post_ln[0], w.post_ln[1], c.layer_norm_eps, out=feats)
+        return feats
+
+    # -- projector ---------------------------------------------------------------------------------------------
+    def project(self, feats: torch.Tensor, proj: "ProjectorWeights | None" = None, out: torch.Tensor | None = None,
+                out_row_map: torch.Tensor | None = None) -> torch.Tensor:
+        """MLPProjector on [M', D] features.  With (out, out_row_map) the last GEMM's epilogue scatters each row
+        to out.view(-1,H)[out_row_map[m]] (splice fused; model.py:441-444)."""
+        p = proj or self.w.proj
+        a = ops.gemm_bias_act(feats, p.w0, p.b0, act=ops.ACT_GELU_ERF)
+        b = ops.gemm_bias_act(a, p.w2, p.b2, act=ops.ACT_GELU_ERF)
+        if out is None:
+            return ops.gemm_bias_act(b, p.w4, p.b4)
+        assert out.dtype == torch.bfloat16 and out.is_contiguous()
+        ops.gemm_bias_act(b, p.w4, p.b4, out=out.view(-1, p.hidden), out_row_map=out_row_map)
+        return out
+
+    def forward(self, pixels: torch.Tensor) -> torch.Tensor:
+        """image_modality.py:130-137 -> [B, P, H] bf16."""
+        B = pixels.shape[0]
+        y = self.project(self.features(pixels))
+        return y.view(B, self.cfg.num_patches, -1)

@@ -1,0 +1,201 @@
+"""Generate tests/golden/*.npz from the UNMODIFIED reference run in this container (TEST INFRASTRUCTURE).
+
+    python -m oracle.make_golden            # needs /root/reference; writes tests/golden/
+
+What is pinned:
+  modality_<tower>.npz   reference ImageModality.forward (HF CLIPVisionTransformer + reference MLPProjector) on
+                         seeded pixels/weights: fp32 run and pure-bf16 run (regime (i), §8 C5), plus taps for `tiny`
+  splice.npz             reference MultiModalModelForCausalLM.embed_modalities_with_text (model.py:410-446) on
+                         seeded cases: right/left padding, 0/1/4 images per row, image at position 0 / at the end,
+                         fp32<->bf16 casts
+  token_range.npz        reference PromptTokenizer.compute_token_range (prompt_tokenizers.py:255-286) + the collator's
+                         index expansion statements (data_loader.py:136-141)
+Weights/pixels are regenerated from (config, seed) by multimeditron_b200.synth at test time, so only outputs are stored.
+The script also asserts that oracle/*.py reproduces the reference bit-for-bit on this CPU.
+"""
+from __future__ import annotations
+
+import os
+import sys
+import tempfile
+import types
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from multimeditron_b200 import synth  # noqa: E402
+from multimeditron_b200.configs import TOWERS  # noqa: E402
+from oracle import ref_shim, splice_oracle, vit_oracle  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+MODALITY_CASES = {  # tower -> (llm hidden, batch, weight seed, pixel seed)
+    "tiny": (64, 4, 11, 3),
+    "clip_b32": (512, 8, 0, 0),   # BASELINE.json configs[0]
+}
+
+
+def bf16_bits(t: torch.Tensor) -> np.ndarray:
+    return t.contiguous().view(torch.int16).numpy()
+
+
+def build_reference_modality(ref, cfg, hidden, sd):
+    from transformers import CLIPConfig, CLIPImageProcessor, CLIPModel
+    tmp = tempfile.mkdtemp(prefix="clip_ckpt_")
+    vc = dict(hidden_size=cfg.hidden_size, intermediate_size=cfg.intermediate_size,
+              num_hidden_layers=cfg.num_hidden_layers, num_attention_heads=cfg.num_attention_heads,
+              image_size=cfg.image_size, patch_size=cfg.patch_size, layer_norm_eps=cfg.layer_norm_eps,
+              hidden_act=cfg.hidden_act)
+    tc = dict(hidden_size=32, intermediate_size=64, num_hidden_layers=1, num_attention_heads=2, vocab_size=64,
+              max_position_embeddings=16)
+    CLIPModel(CLIPConfig(vision_config=vc, text_config=tc, projection_dim=32)).save_pretrained(tmp)
+    CLIPImageProcessor(size={"shortest_edge": cfg.image_size},
+                       crop_size={"height": cfg.image_size, "width": cfg.image_size}).save_pretrained(tmp)
+    from multimeditron.model.modalities.image_modality import ImageConfig, ImageModality
+    m = ImageModality(ImageConfig(hidden_size=hidden, clip_name=tmp))
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not unexpected, unexpected
+    assert all(not k.startswith(("feature_extractor.vision_model", "projector")) for k in missing), missing
+    return m.eval()
+
+
+@torch.no_grad()
+def gen_modality(ref):
+    for name, (hidden, batch, wseed, pseed) in MODALITY_CASES.items():
+        cfg = TOWERS[name]
+        sd32 = synth.make_modality_state_dict(cfg, hidden, seed=wseed)
+        pixels = synth.make_pixels(cfg, batch, seed=pseed)
+        inputs = [pixels[i] for i in range(batch)]
+        out = {}
+        m = build_reference_modality(ref, cfg, hidden, sd32).float()
+        # ---- fp32 reference run + module-boundary taps via forward hooks
+        taps_ref = {}
+        vm = m.feature_extractor.vision_model
+        hooks = [vm.embeddings.register_forward_hook(lambda _m, _i, o: taps_ref.__setitem__("embeddings", o)),
+                 vm.encoder.layers[0].register_forward_hook(lambda _m, _i, o: taps_ref.__setitem__("layer0", o)),
+                 vm.encoder.layers[-1].register_forward_hook(
+                     lambda _m, _i, o: taps_ref.__setitem__(f"layer{cfg.num_hidden_layers - 1}", o))]
+        y32 = m(inputs)
+        for h in hooks:
+            h.remove()
+        taps = {}
+        o32 = vit_oracle.image_modality_forward(sd32, cfg, inputs, taps)
+        assert torch.equal(y32, o32), f"{name}: oracle != reference (fp32)"
+        for k, v in taps_ref.items():
+            v = v[0] if isinstance(v, tuple) else v
+            assert torch.equal(v, taps[k]), f"{name}: tap {k} differs"
+        out["out_fp32"] = y32.numpy()
+        if name == "tiny":
+            for k in ("embeddings", "layer0", f"layer{cfg.num_hidden_layers - 1}", "features"):
+                out["tap_" + k] = taps[k].numpy()
+        # ---- pure-bf16 module run (regime (i): training dtype, every op rounds to bf16)
+        mb = m.to(torch.bfloat16)
+        yb = mb(inputs)
+        sdb = {k: v.to(torch.bfloat16) for k, v in sd32.items()}
+        ob = vit_oracle.image_modality_forward(sdb, cfg, inputs)
+        assert torch.equal(yb, ob), f"{name}: oracle != reference (bf16)"
+        out["out_bf16_bits"] = bf16_bits(yb)
+        err = (yb.float() - y32).abs().max().item()
+        print(f"[modality {name}] out {tuple(y32.shape)} absmax {y32.abs().max():.4f} bf16-vs-fp32 maxabs {err:.3e}")
+        np.savez_compressed(os.path.join(GOLD, f"modality_{name}.npz"), hidden=hidden, batch=batch, wseed=wseed,
+                            pseed=pseed, **out)
+
+
+SPLICE_CASES = [
+    # name, batch, seq, images/row, tokens/image, hidden, padding, min_len, table dtype, proj dtype
+    ("right_1img", 3, 40, 1, 9, 32, "right", 24, "float32", "float32"),
+    ("left_4img", 4, 96, 4, 9, 32, "left", 60, "float32", "float32"),
+    ("noimg_rows", 5, 48, 2, 4, 16, "right", 20, "float32", "float32"),
+    ("img_at_edges", 2, 22, 2, 9, 16, "right", 22, "float32", "float32"),
+    ("bf16_table_f32_proj", 3, 40, 2, 9, 32, "left", 30, "bfloat16", "float32"),
+    ("f32_table_bf16_proj", 3, 40, 2, 9, 32, "right", 30, "float32", "bfloat16"),
+    ("bf16_both", 4, 64, 3, 9, 64, "right", 40, "bfloat16", "bfloat16"),
+]
+VOCAB, ATT, START, END, PAD = 97, 3, 4, 5, 0
+
+
+def splice_case_inputs(case):
+    name, B, S, n_img, tpi, H, side, min_len, tdt, pdt = case
+    seed = sum(map(ord, name))
+    ids, mask = synth.make_sequences(B, S, n_img, tpi, VOCAB, ATT, START, END, PAD, seed=seed, padding_side=side,
+                                     min_len=min_len)
+    if name == "noimg_rows":      # rows 1 and 3 carry no image at all
+        for b in (1, 3):
+            row = ids[b]
+            row[(row == ATT) | (row == START) | (row == END)] = 11
+    if name == "img_at_edges":    # image block at position 0 of row 0 and flush at the end of row 1
+        blk = torch.tensor([START] + [ATT] * tpi + [END])
+        ids[0] = torch.cat([blk, torch.full((S - len(blk),), 13)])
+        ids[1] = torch.cat([torch.full((S - len(blk),), 17), blk])
+    gen = torch.Generator().manual_seed(seed)
+    table = (torch.randn(VOCAB, H, generator=gen) * 0.02).to(getattr(torch, tdt))
+    n_mod = int((ids == ATT).sum())
+    proj = torch.randn(n_mod // tpi, tpi, H, generator=gen).to(getattr(torch, pdt))
+    return ids, table, proj, tpi
+
+
+@torch.no_grad()
+def gen_splice(ref):
+    Model = ref.model.MultiModalModelForCausalLM
+    pt_cls = ref.prompt_tokenizers
+    tok_cls = [getattr(pt_cls, n) for n in dir(pt_cls) if hasattr(getattr(pt_cls, n), "compute_token_range")][0]
+    out, tr_out = {}, {}
+    for case in SPLICE_CASES:
+        name = case[0]
+        ids, table, proj, tpi = splice_case_inputs(case)
+        # --- indices exactly as the reference builds them: compute_token_range per row + collator expansion
+        fake_tok = types.SimpleNamespace(attachment_token_idx=ATT, get_num_embeddings=lambda m: m["num_embeddings"])
+        ranges = []
+        for b in range(ids.shape[0]):
+            n_img = int((ids[b] == ATT).sum()) // tpi
+            mods = [{"num_embeddings": tpi, "type": "image"} for _ in range(n_img)]
+            ranges.append(tok_cls.compute_token_range(fake_tok, ids[b], mods))
+        multi = [(b, tr) for b, rs in enumerate(ranges) for tr in rs]
+        if multi:   # data_loader.py:136-139, same statements
+            batch_idx, token_range = zip(*multi)
+            bidx = torch.tensor(batch_idx).repeat_interleave(torch.tensor([tr[1] - tr[0] for tr in token_range]))
+            trng = torch.cat([torch.tensor(range(tr[0], tr[1])) for tr in token_range])
+        else:
+            bidx = trng = torch.zeros(0, dtype=torch.int64)
+        # oracle restatement must agree with the reference's statements
+        o_ranges = [splice_oracle.compute_token_range(ids[b].numpy(), [tpi] * (int((ids[b] == ATT).sum()) // tpi), ATT)
+                    for b in range(ids.shape[0])]
+        assert o_ranges == [[tuple(map(int, r)) for r in rs] for rs in ranges], name
+        ob, ot = splice_oracle.collator_indices(o_ranges)
+        assert np.array_equal(ob, bidx.numpy()) and np.array_equal(ot, trng.numpy()), name
+        dest, _ = splice_oracle.attach_positions(ids.numpy(), ATT)
+        assert np.array_equal(dest, (bidx * ids.shape[1] + trng).numpy().astype(np.int32)), name
+        # --- the reference's own embed_modalities_with_text on a minimal stand-in for `self`
+        emb = torch.nn.Embedding(VOCAB, table.shape[1], _weight=table.clone())
+        fake_self = types.SimpleNamespace(
+            model=types.SimpleNamespace(get_input_embeddings=lambda: emb),
+            _get_modality_by_name=lambda n: (lambda stack: proj))
+        pmi = {"stacked": {"image": [None]}, "batch_idx": {"image": bidx}, "token_range": {"image": trng}}
+        y = Model.embed_modalities_with_text(fake_self, ids, pmi)
+        o = splice_oracle.embed_modalities_with_text(table, ids, bidx, trng, proj)
+        assert torch.equal(y, o), name
+        out[name + "__ids"] = ids.numpy()
+        out[name + "__bidx"] = bidx.numpy()
+        out[name + "__trng"] = trng.numpy()
+        out[name + "__out"] = bf16_bits(y) if y.dtype == torch.bfloat16 else y.numpy()
+        tr_out[name + "__ranges"] = np.array([(b, s, e) for b, rs in enumerate(ranges) for (s, e) in rs],
+                                             dtype=np.int64).reshape(-1, 3)
+        print(f"[splice {name}] ids {tuple(ids.shape)} n_mod {bidx.numel()} out {tuple(y.shape)} {y.dtype}")
+    np.savez_compressed(os.path.join(GOLD, "splice.npz"), **out)
+    np.savez_compressed(os.path.join(GOLD, "token_range.npz"), **tr_out)
+
+
+def main():
+    os.makedirs(GOLD, exist_ok=True)
+    torch.manual_seed(0)
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    ref = ref_shim.import_reference()
+    gen_splice(ref)
+    gen_modality(ref)
+    print("golden written to", GOLD)
+
+
+if __name__ == "__main__":
+    main()
