@@ -1,0 +1,309 @@
+#!/usr/bin/env python
+"""bench.py — image-embed tokens/s of the modality-embedding hot path (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # B200 arm  (one process per GPU under torchrun for N>1)
+    python bench.py --impl reference --gpus N --steps K ...   # reference arm: the CPU restatement on the host cores
+
+Workload (config.workload): BASELINE.json configs[1] — CLIP ViT-L/14-336 + MLP projector into hidden 4096, bf16,
+synthetic 336px images, one image per row of a 642-token sequence (576 attachment tokens + 2 delimiters + 64 text),
+256 images per GPU (weak scaling: the per-GPU batch is fixed, rows are sharded by sample, no collective on the path).
+A step = embed_modalities_with_text over one batch: embedding lookup, patch-embed, 24 encoder layers, projector,
+splice.  `value` has inputs resident in HBM; `e2e` runs the same step through the public embedder call with HOST
+(pinned) buffers, the H2D copies and a D2H read of the result inside the timed region.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC, UNIT = "image_embed_tokens_per_s", "tokens/s"
+WORKLOADS = {
+    # name: (tower, llm hidden, images/GPU, text tokens per row, vocab)
+    "cfg2_clip_l14_336_llama8b": ("clip_l14_336", 4096, 256, 64, 128_258),
+    "cfg1_clip_b32_tiny_llama": ("clip_b32", 512, 8, 4, 206),
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sust=d["bf16_tflops_sustained"], src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def build_inputs(wl, seed, images, torch, synth, TOWERS):
+    tower, H, _, n_text, V = WORKLOADS[wl]
+    cfg = TOWERS[tower]
+    S = cfg.num_patches + 2 + n_text
+    att, start, end, pad = V - 2, V - 4, V - 3, V - 1   # the added special tokens sit at the end of the vocabulary
+    ids, _ = synth.make_sequences(images, S, 1, cfg.num_patches, V - 4, att, start, end, pad, seed=seed)
+    px = synth.make_pixels(cfg, images, seed=seed)
+    return cfg, H, V, S, att, ids, px
+
+
+def cpu_reference_leg(wl, sample_images, steps, warmup, threads, dtype_name="float32"):
+    """The reference's CPU path (oracle port: same torch ops as HF CLIP + reference projector + splice) on the host
+    cores, on a bounded sample of the workload.  Returns (tokens/s, ms_per_step, description)."""
+    import torch
+    from multimeditron_b200 import synth
+    from multimeditron_b200.configs import TOWERS
+    from oracle import splice_oracle, vit_oracle
+    torch.set_num_threads(threads)
+    cfg, H, V, S, att, ids, px = build_inputs(wl, 0, sample_images, torch, synth, TOWERS)
+    dt = getattr(torch, dtype_name)
+    sd = {k: v.to(dt) for k, v in synth.make_modality_state_dict(cfg, H, seed=0).items()}
+    table = (torch.randn(V, H, generator=torch.Generator().manual_seed(1)) * 0.02).to(dt)
+    ranges = [splice_oracle.compute_token_range(ids[b].numpy(), [cfg.num_patches], att) for b in range(sample_images)]
+    bidx, trng = map(torch.from_numpy, splice_oracle.collator_indices(ranges))
+    inputs = [px[i] for i in range(sample_images)]
+
+    def step():
+        with torch.no_grad():
+            proj = vit_oracle.image_modality_forward(sd, cfg, inputs)
+            return splice_oracle.embed_modalities_with_text(table, ids, bidx, trng, proj)
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt_s = (time.perf_counter() - t0) / steps
+    toks = sample_images * cfg.num_patches / dt_s
+    desc = (f"{sample_images} of {WORKLOADS[wl][2]} images per step ({dtype_name}, torch CPU ops, {threads} threads), "
+            f"full path incl. embedding+splice of those rows")
+    return toks, dt_s * 1e3, desc
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    sample = args.cpu_sample
+    toks, ms, desc = cpu_reference_leg(args.workload, sample, max(1, args.steps), max(0, min(args.warmup, 1)), threads)
+    tower, H, ipg, n_text, V = WORKLOADS[args.workload]
+    line = {"impl": "reference", "metric": METRIC, "value": toks, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic (seeded N(0,1) pixels, random-init weights)",
+            "config": {"workload": args.workload, "tower": tower, "llm_hidden": H, "images_per_gpu": ipg,
+                       "sample": desc},
+            "cpu_baseline": {"value": toks, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc},
+            "e2e": {"value": toks, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from multimeditron_b200 import ops, sharding, synth
+    from multimeditron_b200.configs import TOWERS
+    from multimeditron_b200.modalities import AutoModality
+    from multimeditron_b200.model import B200MultiModalEmbedder
+
+    rank, local_rank, world = sharding.env_rank_world()
+    assert torch.cuda.is_available(), "bench.py (B200 arm) needs a CUDA device; there is no CPU fallback"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    tower, H, images, n_text, V = WORKLOADS[args.workload]
+    if args.images_per_gpu:
+        images = args.images_per_gpu
+    cfg, H, V, S, att, ids, px = build_inputs(args.workload, 100 + rank, images, torch, synth, TOWERS)
+    P = cfg.num_patches
+
+    # weights: replicated on every GPU (same seed), random init of the named architecture
+    sd = synth.make_modality_state_dict(cfg, H, seed=0, dtype=torch.bfloat16)
+    mcfg = AutoModality.config_from_dict({"model_type": "meditron_clip_b200", "hidden_size": H, "clip_name": tower})
+    modality = AutoModality.from_config(mcfg).load_reference_state_dict(sd, dev)
+    del sd
+    table = (torch.randn(V, H, generator=torch.Generator().manual_seed(1)) * 0.02).bfloat16().to(dev)
+    embedder = B200MultiModalEmbedder(table, [modality], att)
+
+    # ---- device-resident inputs for `value`
+    ids_d, px_d = ids.to(dev), px.to(dev)
+    pmi_dev = {"stacked": {"image": px_d}, "batch_idx": {}, "token_range": {}}
+    # ---- host (pinned) inputs for `e2e`
+    ids_h, px_h = ids.pin_memory(), px.pin_memory()
+    pmi_host = {"stacked": {"image": px_h}, "batch_idx": {}, "token_range": {}}
+    result_h = torch.empty(H, dtype=torch.bfloat16).pin_memory()
+    status_h = torch.empty(1, dtype=torch.int32).pin_memory()
+
+    def step_dev():
+        return embedder(ids_d, pmi_dev, positions_from="device")
+
+    def step_e2e():
+        out = embedder(ids_h, pmi_host, positions_from="device")       # H2D of ids + pixels inside
+        result_h.copy_(out.view(-1, H)[-1], non_blocking=True)          # D2H read of the step's result (last row)
+        status_h.copy_(embedder.status(), non_blocking=True)            # + the data-dependent error word
+        return out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        return sharding.max_over_ranks(e0.elapsed_time(e1) / steps, dev)
+
+    warm = max(3, args.warmup)
+    for _ in range(warm):
+        step_dev()
+    torch.cuda.synchronize()
+    embedder.check()
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    # ---- timed region (device-resident inputs), per-op CUDA events recorded on the launching stream
+    ops.LAUNCHES = 0
+    ops.profile_start()
+    ms = timed(step_dev, args.steps)
+    prof = ops.profile_stop()
+    launches_per_step = ops.LAUNCHES // args.steps
+    clocks = sampler.stop() if sampler else None
+    # ---- e2e region (host buffers)
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+    embedder.check()
+    assert int(status_h.item()) == 0
+
+    # ---- splice standalone (BASELINE metric 'splice HBM GB/s'): in-place scatter of B*P rows x H bf16
+    proj = torch.randn(images * P, H, device=dev).bfloat16()
+    dest_rows, _, _ = ops.attach_positions(ids_d, att, expected_rows=images * P, want_src_of_pos=False)
+    emb = ops.embed_gather(table, ids_d)
+    for _ in range(3):
+        ops.splice_scatter(emb.view(-1, H), proj, dest_rows)
+    ms_sp = timed(lambda: ops.splice_scatter(emb.view(-1, H), proj, dest_rows), max(10, args.steps))
+    splice_bytes = 2.0 * images * P * H * 2
+    del proj, emb
+
+    total_images = images * world
+    pk = peaks()
+    flops_img = cfg.flops_per_image(H)
+    n_gemm, ms_gemm, fl_gemm = prof.get("mm_gemm_bias_act", (0, 0.0, 0.0))
+    gemm_tf = fl_gemm / (ms_gemm * 1e-3) / 1e12 if ms_gemm else 0.0
+    path_tf = flops_img * images / (ms * 1e-3) / 1e12
+    line = {
+        "metric": METRIC, "value": total_images * P / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic (seeded N(0,1) pixels, random-init weights; no network for checkpoints)",
+        "config": {"workload": args.workload, "tower": tower, "llm_hidden": H, "images_per_gpu": images,
+                   "global_images": total_images, "seq_len": S, "tokens_per_image": P, "parallelism": f"sample-shard x{world}",
+                   "l2": "inputs larger than L2 (pixels %.0f MB, inputs_embeds %.0f MB per step)" % (
+                       px.numel() * 4 / 1e6, images * S * H * 2 / 1e6),
+                   "positions": "device prefix sum", "splice": "fused into the last projector GEMM epilogue"},
+        "clocks": clocks,
+        "e2e": {"value": total_images * P / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": int(px.numel() * 4 + ids.numel() * 8), "d2h_bytes_per_step": int(H * 2 + 4)},
+        "gpu_launches": launches_per_step * args.steps,
+        "gpu_launches_per_step": launches_per_step,
+        "roofline": {"kernel": "gemm_bf16_tn_kernel<false> (tcgen05 GEMM, %d launches/step)" % (n_gemm // max(1, args.steps)),
+                     "bound": "tensor", "achieved": gemm_tf, "peak": pk["tf_sust"], "unit": "TFLOP/s",
+                     "frac": gemm_tf / pk["tf_sust"], "traffic": None,
+                     "peak_kind": f"{pk['src']} sustained cuBLAS bf16 (kernel timed inside a long step)",
+                     "frac_of_burst": gemm_tf / pk["tf_burst"]},
+        "path_tensor": {"achieved": path_tf, "unit": "TFLOP/s", "frac_of_sustained": path_tf / pk["tf_sust"],
+                        "frac_of_burst": path_tf / pk["tf_burst"], "gflop_per_image": flops_img / 1e9,
+                        "note": "algorithmic FLOPs of the whole path / whole step time (attention, LN, patch, splice included)"},
+        "roofline_splice": {"kernel": "move_rows_kernel<0> (mm_splice_scatter, standalone)", "bound": "hbm",
+                            "achieved": splice_bytes / (ms_sp * 1e-3) / 1e9, "peak": pk["hbm"], "unit": "GB/s",
+                            "frac": splice_bytes / (ms_sp * 1e-3) / 1e9 / pk["hbm"], "bytes": splice_bytes,
+                            "ms": ms_sp, "traffic": None},
+        "op_ms_per_step": {k: v[1] / args.steps for k, v in sorted(prof.items())},
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        toks, _, desc = cpu_reference_leg(args.workload, args.cpu_sample, 1, 1, threads)
+        line["cpu_baseline"] = {"value": toks, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg2_clip_l14_336_llama8b", choices=list(WORKLOADS))
+    ap.add_argument("--images-per-gpu", type=int, default=0)
+    ap.add_argument("--cpu-sample", type=int, default=4, help="images per CPU-baseline step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -88,6 +88,8 @@ class B200ImageModality(BaseModality):
         self.embedding_size = self.tower.hidden_size
         self._num_patches_per_entry = self.tower.num_patches
         self._runner: Optional[TowerRunner] = None
+        self._staging: Optional[torch.Tensor] = None
+        self._staging_event = None
         self._frozen = True
         if state_dict is not None:
             self.load_reference_state_dict(state_dict, device or torch.device("cuda", torch.cuda.current_device()))
@@ -123,9 +125,21 @@ class B200ImageModality(BaseModality):
         inputs = list(inputs)
         if len(inputs) and inputs[0].is_cuda:
             return torch.stack(inputs, dim=0)
-        # one pinned staging buffer + one async H2D instead of the reference's pageable, synchronous copy (:131-132)
-        stacked = torch.stack(inputs, dim=0)
-        return stacked.pin_memory().to(dev, non_blocking=True) if stacked.numel() else stacked.to(dev)
+        # one cached pinned staging buffer + one async H2D instead of the reference's pageable, synchronous
+        # copy (:131-132)
+        if not inputs:
+            return torch.empty(0, 3, self.tower.image_size, self.tower.image_size, device=dev)
+        shape, dt = (len(inputs), *inputs[0].shape), inputs[0].dtype
+        buf = self._staging
+        if buf is None or buf.shape != shape or buf.dtype != dt:
+            buf = self._staging = torch.empty(shape, dtype=dt, pin_memory=True)
+        if self._staging_event is not None:
+            self._staging_event.synchronize()  # the previous H2D out of this buffer must have finished
+        torch.stack(inputs, dim=0, out=buf)
+        out = buf.to(dev, non_blocking=True)
+        self._staging_event = torch.cuda.Event()
+        self._staging_event.record()
+        return out
 
     @torch.no_grad()
     def forward(self, inputs: List[torch.Tensor]) -> torch.Tensor:

@@ -22,6 +22,45 @@ class MMError(RuntimeError):
     pass
 
 
+# -- instrumentation (bench.py): kernel-launch counter and optional per-op CUDA-event timing --------------------
+KERNELS_PER_CALL = {"mm_attach_positions": 3, "mm_patch_embed": 2}
+LAUNCHES = 0
+_PROFILE = None  # dict: op name -> list[(start_event, end_event, work)] when enabled
+
+
+def profile_start():
+    global _PROFILE
+    _PROFILE = {}
+
+
+def profile_stop():
+    """-> {op: (n_calls, total_ms, total_work)}; synchronises."""
+    global _PROFILE
+    prof, _PROFILE = _PROFILE, None
+    torch.cuda.synchronize()
+    return {k: (len(v), sum(a.elapsed_time(b) for a, b, _ in v), sum(w for _, _, w in v)) for k, v in (prof or {}).items()}
+
+
+class _timed:
+    def __init__(self, name, work=0.0):
+        self.name, self.work = name, work
+
+    def __enter__(self):
+        global LAUNCHES
+        LAUNCHES += KERNELS_PER_CALL.get(self.name, 1)
+        if _PROFILE is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *a):
+        if _PROFILE is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            _PROFILE.setdefault(self.name, []).append((self.e0, e1, self.work))
+        return False
+
+
 def _dt(t: torch.Tensor) -> int:
     if t.dtype == torch.bfloat16:
         return MM_BF16
@@ -80,7 +119,8 @@ def attach_positions(input_ids: torch.Tensor, attachment_id: int, expected_rows:
     sop = torch.empty(max(n, 1), dtype=torch.int32, device=dev) if want_src_of_pos else None
     count = torch.empty(1, dtype=torch.int32, device=dev)
     ws = torch.empty(lib.mm_attach_positions_workspace_bytes(n), dtype=torch.uint8, device=dev)
-    rc = lib.mm_attach_positions(_ptr(ids), n, int(attachment_id), _ptr(dest_rows), cap, _ptr(sop), _ptr(count),
+    with _timed("mm_attach_positions", float(n) * 8):
+        rc = lib.mm_attach_positions(_ptr(ids), n, int(attachment_id), _ptr(dest_rows), cap, _ptr(sop), _ptr(count),
                                  int(expected_rows), _ptr(status), _ptr(ws), _stream())
     _check(rc, "mm_attach_positions")
     return dest_rows[:cap], (sop[:n] if sop is not None else None), count
@@ -96,7 +136,8 @@ def splice_scatter(dest: torch.Tensor, src: torch.Tensor, dest_rows: torch.Tenso
     assert dest_rows.dtype == torch.int32 and dest_rows.is_contiguous()
     n_rows = src.numel() // H if H else 0
     assert dest_rows.numel() >= n_rows
-    rc = lib.mm_splice_scatter(_ptr(dest), dest.numel() // H if H else 0, H, _dt(dest), _ptr(src), n_rows, _dt(src),
+    with _timed("mm_splice_scatter", 2.0 * n_rows * H * src.element_size()):
+        rc = lib.mm_splice_scatter(_ptr(dest), dest.numel() // H if H else 0, H, _dt(dest), _ptr(src), n_rows, _dt(src),
                                _ptr(dest_rows), _ptr(status), _stream())
     _check(rc, "mm_splice_scatter")
     return dest
@@ -117,7 +158,8 @@ def splice_scatter_idx(dest: torch.Tensor, src: torch.Tensor, batch_idx: torch.T
             f"shape [{batch_idx.numel()}, {H}]")
     bi = batch_idx.contiguous().to(torch.int64)
     tr = token_range.contiguous().to(torch.int64)
-    rc = lib.mm_splice_scatter_idx(_ptr(dest), B, S, H, _dt(dest), _ptr(src), n_rows, _dt(src), _ptr(bi), _ptr(tr),
+    with _timed("mm_splice_scatter_idx", 2.0 * n_rows * H * src.element_size()):
+        rc = lib.mm_splice_scatter_idx(_ptr(dest), B, S, H, _dt(dest), _ptr(src), n_rows, _dt(src), _ptr(bi), _ptr(tr),
                                    _ptr(status), _stream())
     _check(rc, "mm_splice_scatter_idx")
     return dest
@@ -129,7 +171,8 @@ def embed_gather(table: torch.Tensor, input_ids: torch.Tensor, status: torch.Ten
     V, H = table.shape
     ids = input_ids.contiguous()
     out = torch.empty(*ids.shape, H, dtype=table.dtype, device=table.device)
-    rc = lib.mm_embed_gather(_ptr(out), ids.numel(), H, _dt(table), _ptr(table.contiguous()), V, _ptr(ids),
+    with _timed("mm_embed_gather", 2.0 * ids.numel() * H * table.element_size()):
+        rc = lib.mm_embed_gather(_ptr(out), ids.numel(), H, _dt(table), _ptr(table.contiguous()), V, _ptr(ids),
                              _ptr(status), _stream())
     _check(rc, "mm_embed_gather")
     return out
@@ -144,7 +187,8 @@ def embed_splice_fused(table: torch.Tensor, input_ids: torch.Tensor, src_of_pos:
     if out is None:
         out = torch.empty(*ids.shape, H, dtype=table.dtype, device=table.device)
     n_rows = src.numel() // H if H else 0
-    rc = lib.mm_embed_splice_fused(_ptr(out), ids.numel(), H, _dt(out), _ptr(table.contiguous()), V, _ptr(ids),
+    with _timed("mm_embed_splice_fused", 2.0 * ids.numel() * H * out.element_size()):
+        rc = lib.mm_embed_splice_fused(_ptr(out), ids.numel(), H, _dt(out), _ptr(table.contiguous()), V, _ptr(ids),
                                    _ptr(src_of_pos), _ptr(src.contiguous()), n_rows, _dt(src), _ptr(status),
                                    _stream())
     _check(rc, "mm_embed_splice_fused")
@@ -161,7 +205,8 @@ def layernorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: flo
     if out is None:
         out = torch.empty_like(x)
     M = out.numel() // D
-    rc = lib.mm_layernorm(_ptr(x), _ptr(out), _ptr(gamma), _ptr(beta), M, D, float(eps), rows_in_group,
+    with _timed("mm_layernorm", 4.0 * M * D):
+        rc = lib.mm_layernorm(_ptr(x), _ptr(out), _ptr(gamma), _ptr(beta), M, D, float(eps), rows_in_group,
                           rows_out_group, in_row_offset, _stream())
     _check(rc, "mm_layernorm")
     return out
@@ -184,7 +229,8 @@ def gemm_bias_act(a: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = 
     assert out.dtype == torch.bfloat16 and out.stride(-1) == 1
     ldc = out.stride(-2) if out.dim() >= 2 else N
     ldr = residual.stride(-2) if residual is not None else 0
-    rc = lib.mm_gemm_bias_act(_ptr(a), a.stride(0), _ptr(w), w.stride(0), _ptr(bias), _ptr(out), ldc, M, N, K,
+    with _timed("mm_gemm_bias_act", 2.0 * M * N * K):
+        rc = lib.mm_gemm_bias_act(_ptr(a), a.stride(0), _ptr(w), w.stride(0), _ptr(bias), _ptr(out), ldc, M, N, K,
                               int(act), _ptr(residual), ldr, int(res_mod), int(res_row_off), _ptr(out_row_map),
                               _stream())
     _check(rc, "mm_gemm_bias_act")
@@ -202,7 +248,8 @@ def patch_embed(pixels: torch.Tensor, weight_padded: torch.Tensor, conv_bias, po
     T = pos_emb.shape[0]
     if out is None:
         out = torch.empty(B, T, D, dtype=torch.bfloat16, device=pixels.device)
-    rc = lib.mm_patch_embed(_ptr(pixels), _dt(pixels), B, img, patch, _ptr(weight_padded), weight_padded.stride(0),
+    with _timed("mm_patch_embed", 2.0 * B * (T - (1 if cls is not None else 0)) * D * 3 * patch * patch):
+        rc = lib.mm_patch_embed(_ptr(pixels), _dt(pixels), B, img, patch, _ptr(weight_padded), weight_padded.stride(0),
                             _ptr(conv_bias), _ptr(pos_emb), _ptr(cls), _ptr(out), D, _stream())
     _check(rc, "mm_patch_embed")
     return out
@@ -216,7 +263,8 @@ def attention_fwd(qkv: torch.Tensor, B: int, T: int, heads: int, head_dim: int, 
     assert qkv.dtype == torch.bfloat16 and qkv.is_contiguous() and qkv.numel() == B * T * 3 * D
     if out is None:
         out = torch.empty(B * T, D, dtype=torch.bfloat16, device=qkv.device)
-    rc = lib.mm_attention_fwd(_ptr(qkv), _ptr(out), B, T, heads, head_dim, float(scale), _stream())
+    with _timed("mm_attention_fwd", 4.0 * B * heads * T * T * head_dim):
+        rc = lib.mm_attention_fwd(_ptr(qkv), _ptr(out), B, T, heads, head_dim, float(scale), _stream())
     _check(rc, "mm_attention_fwd")
     return out
 
@@ -228,6 +276,7 @@ def weighted_expert_sum(x: torch.Tensor, w: torch.Tensor, perm: torch.Tensor | N
     E, R, D = x.shape
     assert R == B * P and x.is_contiguous() and w.dtype == torch.float32 and w.is_contiguous()
     out = torch.empty(R, D, dtype=torch.bfloat16, device=x.device)
-    rc = lib.mm_weighted_expert_sum(_ptr(x), _ptr(w), _ptr(perm), _ptr(out), E, B, P, D, _stream())
+    with _timed("mm_weighted_expert_sum", 2.0 * (E + 1) * R * D):
+        rc = lib.mm_weighted_expert_sum(_ptr(x), _ptr(w), _ptr(perm), _ptr(out), E, B, P, D, _stream())
     _check(rc, "mm_weighted_expert_sum")
     return out

@@ -1,0 +1,160 @@
+"""-m gpu: floating-point kernels through the C-ABI vs a plain PyTorch fp32 reference of the same op.
+
+Tolerance (stated, bf16 storage / fp32 accumulate): |got-ref| <= 2e-2*max|ref| + 1.6e-2*|ref|  (2 bf16 ulps of the
+largest value + 2 ulps relative) — one bf16 rounding of the output plus bf16-rounded intermediates."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from multimeditron_b200 import ops
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def close(got, ref, tol=2e-2):
+    got, ref = got.float(), ref.float()
+    assert torch.isfinite(got).all()
+    err = (got - ref).abs()
+    lim = tol * ref.abs().max() + 1.6e-2 * ref.abs()
+    bad = err > lim
+    assert not bad.any(), f"max err {err.max().item():.3e}, {int(bad.sum())} bad of {bad.numel()}"
+
+
+@pytest.mark.parametrize("M,D", [(1, 128), (77, 768), (300, 1024), (50, 1152), (4096, 1024)])
+def test_layernorm(M, D):
+    g0 = torch.Generator().manual_seed(M * D)
+    x = (torch.randn(M, D, generator=g0) * 3 + 1).bfloat16().to(DEV)
+    g = (1 + 0.1 * torch.randn(D, generator=g0)).bfloat16().to(DEV)
+    b = (0.1 * torch.randn(D, generator=g0)).bfloat16().to(DEV)
+    for eps in (1e-5, 1e-6):
+        y = ops.layernorm(x, g, b, eps)
+        close(y, F.layer_norm(x.float(), (D,), g.float(), b.float(), eps))
+
+
+def test_layernorm_row_remap_drops_cls():
+    B, T, D = 3, 17, 128
+    x = torch.randn(B * T, D, device=DEV).bfloat16()
+    g = torch.ones(D, device=DEV).bfloat16()
+    b = torch.zeros(D, device=DEV).bfloat16()
+    out = torch.empty(B * (T - 1), D, device=DEV).bfloat16()
+    ops.layernorm(x, g, b, 1e-5, out=out, rows_in_group=T, rows_out_group=T - 1, in_row_offset=1)
+    ref = F.layer_norm(x.float().view(B, T, D)[:, 1:], (D,)).reshape(-1, D)
+    close(out, ref)
+
+
+GEMM_CASES = [
+    # M, N, K, bias, act, residual, rowmap
+    (128, 256, 64, False, 0, False, False),
+    (128, 256, 1024, False, 0, False, False),      # ring wrap
+    (300, 264, 200, False, 0, False, False),       # M/N/K tails
+    (1000, 768, 3072, True, 1, False, False),      # CLIP fc1 + QuickGELU
+    (1000, 1024, 1024, True, 0, True, False),      # out_proj + residual
+    (1731, 1024, 4096, True, 2, True, True),       # erf-GELU + residual + row map
+    (50, 1152, 4304, True, 3, False, False),       # SigLIP shapes, tanh-GELU
+    (400, 2304, 768, True, 0, False, False),       # cfg1 fused QKV
+    (56_837, 512, 128, True, 0, False, False),     # many tiles per CTA (TMEM double buffer, persistence)
+    (8, 8, 8, True, 0, False, False),              # minimum
+]
+
+
+@pytest.mark.parametrize("M,N,K,bias,act,residual,rowmap", GEMM_CASES)
+def test_gemm_bias_act(M, N, K, bias, act, residual, rowmap):
+    g0 = torch.Generator().manual_seed(M + 7 * N + 13 * K)
+    a = torch.randn(M, K, generator=g0).bfloat16().to(DEV)
+    w = (torch.randn(N, K, generator=g0) * 0.05).bfloat16().to(DEV)
+    bs = (torch.randn(N, generator=g0) * 0.5).bfloat16().to(DEV) if bias else None
+    res = torch.randn(M, N, generator=g0).bfloat16().to(DEV) if residual else None
+    ref = a.float() @ w.float().t()
+    if bias:
+        ref = ref + bs.float()
+    ref = {0: lambda t: t, 1: lambda t: t * torch.sigmoid(1.702 * t), 2: F.gelu,
+           3: lambda t: F.gelu(t, approximate="tanh")}[act](ref)
+    if residual:
+        ref = ref + res.float()
+    if rowmap:
+        perm = torch.randperm(M, generator=g0).int().to(DEV)
+        perm[::7] = -1
+        out = torch.full((M, N), 7.0, device=DEV).bfloat16()
+        ops.gemm_bias_act(a, w, bs, act, residual=res, out=out, out_row_map=perm)
+        want = torch.full((M, N), 7.0, device=DEV)
+        keep = perm >= 0
+        want[perm[keep].long()] = ref[keep]
+        close(out, want)
+    else:
+        close(ops.gemm_bias_act(a, w, bs, act, residual=res), ref)
+
+
+def test_gemm_modular_residual_and_strided_output():
+    M, N, K, P = 96, 128, 64, 16
+    a = torch.randn(M, K, device=DEV).bfloat16()
+    w = (torch.randn(N, K, device=DEV) * 0.1).bfloat16()
+    pos = torch.randn(P + 1, N, device=DEV).bfloat16()
+    big = torch.zeros(M, 2 * N, device=DEV).bfloat16()
+    ops.gemm_bias_act(a, w, residual=pos, res_mod=P, res_row_off=1, out=big[:, N:])
+    m = torch.arange(M, device=DEV)
+    close(big[:, N:], a.float() @ w.float().t() + pos.float()[(m % P) + 1])
+    assert not big[:, :N].any()
+
+
+def test_gemm_rejects_bad_arguments():
+    a = torch.zeros(16, 12, device=DEV).bfloat16()   # K % 8 != 0
+    w = torch.zeros(16, 12, device=DEV).bfloat16()
+    with pytest.raises(ops.MMError):
+        ops.gemm_bias_act(a, w)
+
+
+@pytest.mark.parametrize("B,img,p,D,cls,bias,dt", [
+    (2, 32, 8, 128, True, False, torch.float32),
+    (3, 224, 32, 768, True, False, torch.float32),     # CLIP-B/32
+    (2, 336, 14, 1024, True, False, torch.float32),    # CLIP-L/14-336 (K=588, padded to 640)
+    (2, 56, 14, 256, False, True, torch.bfloat16),     # SigLIP-style: conv bias, no CLS, bf16 pixels
+])
+def test_patch_embed(B, img, p, D, cls, bias, dt):
+    G = img // p
+    T = G * G + (1 if cls else 0)
+    g0 = torch.Generator().manual_seed(img * p)
+    px = torch.randn(B, 3, img, img, generator=g0).to(dt).to(DEV)
+    w = (torch.randn(D, 3, p, p, generator=g0) * 0.02).bfloat16().to(DEV)
+    bs = (torch.randn(D, generator=g0) * 0.1).bfloat16().to(DEV) if bias else None
+    pos = (torch.randn(T, D, generator=g0) * 0.1).bfloat16().to(DEV)
+    c = (torch.randn(D, generator=g0) * 0.1).bfloat16().to(DEV) if cls else None
+    K = 3 * p * p
+    wp = torch.zeros(D, (K + 63) // 64 * 64, device=DEV).bfloat16()
+    wp[:, :K] = w.reshape(D, -1)
+    out = ops.patch_embed(px, wp, bs, pos, c, p)
+    ref = F.conv2d(px.bfloat16().float(), w.float(), bs.float() if bias else None, stride=p).flatten(2).transpose(1, 2)
+    if cls:
+        ref = torch.cat([c.float().expand(B, 1, D), ref], 1)
+    close(out, ref + pos.float())
+
+
+@pytest.mark.parametrize("B,T,nh", [(1, 1, 1), (1, 50, 2), (2, 128, 2), (2, 129, 2), (2, 200, 3), (2, 577, 4), (3, 640, 2),
+                                    (40, 577, 16)])
+def test_attention_fwd(B, T, nh):
+    D = nh * 64
+    g0 = torch.Generator().manual_seed(B * T * nh)
+    qkv = (torch.randn(B * T, 3 * D, generator=g0) * 1.5).bfloat16().to(DEV)
+    out = ops.attention_fwd(qkv, B, T, nh, 64, 0.125)
+    q, k, v = [t.view(B, T, nh, 64).transpose(1, 2).float() for t in qkv.view(B, T, 3 * D).split(D, -1)]
+    ref = F.scaled_dot_product_attention(q, k, v, scale=0.125).transpose(1, 2).reshape(B * T, D)
+    close(out, ref, tol=1e-2)
+
+
+def test_attention_rejects_unsupported_shapes():
+    qkv = torch.zeros(8, 3 * 72, device=DEV).bfloat16()
+    with pytest.raises(ops.MMError):
+        ops.attention_fwd(qkv, 1, 8, 1, 72, 0.1)
+
+
+def test_weighted_expert_sum():
+    E, B, P, D = 5, 3, 7, 64
+    x = torch.randn(E, B * P, D, device=DEV).bfloat16()
+    w = torch.softmax(torch.randn(B, E, device=DEV), -1)
+    perm = torch.tensor([2, 0, 4, 1, 3], dtype=torch.int32, device=DEV)
+    for pm in (None, perm):
+        out = ops.weighted_expert_sum(x, w, pm, B, P)
+        ww = w if pm is None else w[:, pm.long()]
+        st = x.view(E, B, P, D).permute(1, 0, 2, 3)  # [B,E,P,D]
+        ref = (st * ww.to(torch.bfloat16)[:, :, None, None]).sum(1).reshape(B * P, D)
+        close(out, ref, tol=1e-2)

@@ -1,0 +1,131 @@
+"""-m gpu: the whole path (ViT + projector + splice) through the plugin mirror vs the reference goldens / oracle.
+
+Stated tolerance for embedder/projector outputs (bf16 storage, fp32 accumulate), SURVEY.md §8 C4(ii):
+  err_vs_fp32_reference <= 2 x (the reference's own bf16 run's error vs its fp32 run)   and
+  max-abs error / max|ref| <= 2e-2.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from multimeditron_b200 import ops, synth
+from multimeditron_b200.configs import TOWERS
+from multimeditron_b200.modalities import AutoModality, B200ImageConfig, B200ImageModality
+from multimeditron_b200.model import B200MultiModalEmbedder
+from oracle import splice_oracle, vit_oracle
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _modality(name, hidden, wseed):
+    cfg = AutoModality.config_from_dict({"model_type": "meditron_clip_b200", "hidden_size": hidden, "clip_name": name})
+    sd = synth.make_modality_state_dict(TOWERS[name], hidden, seed=wseed)
+    m = AutoModality.from_config(cfg)
+    m.load_reference_state_dict(sd, DEV)
+    return m, sd
+
+
+@pytest.mark.parametrize("name", ["tiny", "clip_b32"])
+def test_modality_forward_vs_reference_golden(golden_dir, name):
+    g = np.load(os.path.join(golden_dir, f"modality_{name}.npz"))
+    hidden, batch = int(g["hidden"]), int(g["batch"])
+    m, _ = _modality(name, hidden, int(g["wseed"]))
+    px = synth.make_pixels(TOWERS[name], batch, seed=int(g["pseed"]))
+    y = m([px[i] for i in range(batch)])                       # CPU fp32 tensors in, like the collator hands them over
+    assert y.shape == (batch, TOWERS[name].num_patches, hidden) and y.dtype == torch.bfloat16 and y.is_cuda
+    ref32 = torch.from_numpy(g["out_fp32"])
+    refbf = torch.from_numpy(g["out_bf16_bits"]).view(torch.bfloat16).float()
+    scale = ref32.abs().max().item()
+    err = (y.float().cpu() - ref32).abs().max().item()
+    ref_err = (refbf - ref32).abs().max().item()
+    rel_mean = ((y.float().cpu() - ref32).abs().mean() / ref32.abs().mean()).item()
+    print(f"[{name}] max-abs {err:.3e} (reference bf16 run: {ref_err:.3e}), max-abs/absmax {err / scale:.3e}, mean-rel {rel_mean:.3e}")
+    assert err <= 2.0 * ref_err + 1e-6
+    assert err / scale <= 2e-2
+
+
+def test_gpu_pixels_and_bf16_pixels_accepted():
+    m, sd = _modality("tiny", 64, 1)
+    px = synth.make_pixels(TOWERS["tiny"], 3, seed=2)
+    a = m([p for p in px])
+    b = m([p.to(DEV) for p in px])
+    assert torch.equal(a, b)
+    with pytest.raises(ValueError):  # HF:models/clip/modeling_clip.py:204-207
+        m([torch.zeros(3, 16, 16)])
+
+
+def _make_batch(B, S, n_img, cfg, V, seed, side):
+    att, start, end, pad = V - 4, V - 3, V - 2, V - 1
+    ids, _ = synth.make_sequences(B, S, n_img, cfg.num_patches, V - 4, att, start, end, pad, seed=seed,
+                                  padding_side=side, min_len=S - 8)
+    ranges = [splice_oracle.compute_token_range(ids[b].numpy(), [cfg.num_patches] * n_img, att) for b in range(B)]
+    bidx, trng = splice_oracle.collator_indices(ranges)
+    px = synth.make_pixels(cfg, B * n_img, seed=seed)
+    pmi = {"stacked": {"image": [px[i] for i in range(B * n_img)]},
+           "batch_idx": {"image": torch.from_numpy(bidx)}, "token_range": {"image": torch.from_numpy(trng)}}
+    return ids, pmi, att, px
+
+
+@pytest.mark.parametrize("table_dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("side", ["right", "left"])
+def test_embed_modalities_with_text_vs_oracle(side, table_dtype):
+    """model.py:410-446 end to end: positions from the collator, from the device prefix sum, fused and unfused —
+    all four must be bit-identical to each other, and the spliced rows bit-identical to the modality output."""
+    cfg = TOWERS["tiny"]
+    H, V, B, S, n_img = 64, 300, 3, 64, 2
+    m, sd = _modality("tiny", H, 3)
+    ids, pmi, att, px = _make_batch(B, S, n_img, cfg, V, 5, side)
+    table = (torch.randn(V, H, generator=torch.Generator().manual_seed(1)) * 0.02).to(table_dtype)
+    outs = []
+    for fuse in (False, True):
+        for pos in ("collator", "device"):
+            e = B200MultiModalEmbedder(table.to(DEV), [m], att, fuse_splice=fuse)
+            outs.append(e(ids, pmi, positions_from=pos))
+            e.check()
+    for o in outs[1:]:
+        assert torch.equal(o, outs[0])
+    out = outs[0].cpu()
+    assert out.shape == (B, S, H) and out.dtype == table_dtype
+    # text rows: exact embedding rows; image rows: exactly the modality output cast to the table dtype
+    proj = m(pmi["stacked"]["image"]).cpu()
+    want = splice_oracle.embed_modalities_with_text(table, ids, pmi["batch_idx"]["image"], pmi["token_range"]["image"], proj)
+    assert torch.equal(out, want)
+    # and the modality output itself is within tolerance of the fp32 oracle
+    with torch.no_grad():
+        ref = vit_oracle.image_modality_forward(sd, cfg, pmi["stacked"]["image"])
+    assert (proj.float() - ref).abs().max().item() <= 2e-2 * ref.abs().max().item()
+
+
+def test_count_mismatch_is_detected_not_truncated():
+    cfg = TOWERS["tiny"]
+    m, _ = _modality("tiny", 64, 3)
+    ids, pmi, att, _ = _make_batch(2, 64, 2, cfg, 300, 6, "right")
+    ids[0, (ids[0] == att).nonzero()[0]] = 1   # one attachment token fewer than modality rows
+    e = B200MultiModalEmbedder(torch.zeros(300, 64, device=DEV).bfloat16(), [m], att)
+    e(ids, pmi, positions_from="device")
+    with pytest.raises(RuntimeError):
+        e.check()
+    pmi["batch_idx"]["image"] = pmi["batch_idx"]["image"][:-1]
+    pmi["token_range"]["image"] = pmi["token_range"]["image"][:-1]
+    e2 = B200MultiModalEmbedder(torch.zeros(300, 64, device=DEV).bfloat16(), [m], att, fuse_splice=False)
+    with pytest.raises(RuntimeError):
+        e2(ids, pmi)
+
+
+def test_clip_l14_336_layerwise_sanity():
+    """BASELINE configs[1] shapes (ViT-L/14-336 -> 4096), 2 images: CUDA path vs the fp32 oracle on CPU."""
+    cfg = TOWERS["clip_l14_336"]
+    m, sd = _modality("clip_l14_336", 4096, 0)
+    px = synth.make_pixels(cfg, 2, seed=0)
+    y = m([px[0], px[1]]).float().cpu()
+    with torch.no_grad():
+        ref = vit_oracle.image_modality_forward(sd, cfg, px)
+        sdb = {k: v.to(torch.bfloat16) for k, v in sd.items()}
+        refb = vit_oracle.image_modality_forward(sdb, cfg, px).float()
+    scale = ref.abs().max().item()
+    err, ref_err = (y - ref).abs().max().item(), (refb - ref).abs().max().item()
+    print(f"[clip_l14_336] max-abs {err:.3e} (reference bf16 run: {ref_err:.3e}) max-abs/absmax {err / scale:.3e}")
+    assert err <= 2.0 * ref_err and err / scale <= 2e-2

@@ -91,3 +91,20 @@ def test_oracle_against_live_hf_tower():
         ref = hf(px).last_hidden_state
         got = vit_oracle.vision_last_hidden_state(sd, cfg, px)
     assert torch.equal(ref, got)
+
+
+def test_c_oracle_agrees_with_numpy_oracle():
+    from oracle import c_oracle
+    rng = np.random.default_rng(0)
+    ids = rng.integers(5, 50, size=(7, 33)).astype(np.int64)
+    ids[rng.random(ids.shape) < 0.3] = 3
+    d_np, s_np = splice_oracle.attach_positions(ids, 3)
+    d_c, s_c = c_oracle.attach_positions(ids, 3)
+    assert np.array_equal(d_np, d_c) and np.array_equal(s_np, s_c)
+    table = rng.standard_normal((50, 16)).astype(np.float32)
+    src = rng.standard_normal((d_np.shape[0], 16)).astype(np.float32)
+    out = c_oracle.embed_splice(table, ids, src, d_np)
+    want = splice_oracle.embed_modalities_with_text(
+        torch.from_numpy(table), torch.from_numpy(ids), torch.from_numpy(d_np.astype(np.int64) // 33),
+        torch.from_numpy(d_np.astype(np.int64) % 33), torch.from_numpy(src)).numpy().reshape(-1, 16)
+    assert np.array_equal(out, want)
