@@ -133,14 +133,14 @@ int mm_layernorm(const void* x, void* y, const void* gamma, const void* beta, in
  *   bias [N] bf16 or NULL, C [*,N] bf16 (ldc).
  *   residual (optional, bf16, ldr): row used = (res_mod>0 ? m % res_mod : m) + res_row_off.
  *     The sum is formed as bf16(bf16(acc+bias) + residual), the reference's rounding points.
- *   out_row_map (optional, int32[M]): C row written for GEMM row m; <0 = row not stored.
+ *   out_row_map (optional, int32[M]): C row written for GEMM row m; <0 or >= n_out_rows = row not stored.
  *     (drop-CLS image_modality.py:133; splice fusion model.py:441-444)
  *   Requirements: K % 8 == 0, N % 8 == 0, 16-byte aligned pointers/leading dimensions.
  */
 int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias,
                      void* C, int64_t ldc, int64_t M, int64_t N, int64_t K, int act,
                      const void* residual, int64_t ldr, int64_t res_mod, int64_t res_row_off,
-                     const int32_t* out_row_map, void* stream);
+                     const int32_t* out_row_map, int64_t n_out_rows, void* stream);
 
 /*
  * mm_patch_embed — im2col-free implicit GEMM of the patch convolution

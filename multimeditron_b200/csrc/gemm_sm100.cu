@@ -47,6 +47,7 @@ struct GemmParams {
   const __nv_bfloat16* residual;
   const int32_t* out_row_map;
   int64_t ldc, ldr;
+  int64_t n_out_rows;  // rows of C that may be written through out_row_map (bounds check)
   int M, N, K;
   int res_mod, res_row_off;
   int map_in, map_out, map_off;  // formula row map: out_row = (m / map_in) * map_out + map_off + m % map_in
@@ -200,7 +201,10 @@ __global__ void __launch_bounds__(kGatherA ? 384 : 256, 1)
       const int my_m = m0 + q * 32 + lane;
       int my_out = -1;
       if (my_m < p.M) {
-        if (p.out_row_map) my_out = p.out_row_map[my_m];
+        if (p.out_row_map) {
+          my_out = p.out_row_map[my_m];
+          if ((int64_t)my_out >= p.n_out_rows) my_out = -1;  // never write outside C
+        }
         else if (p.map_in > 0) my_out = (my_m / p.map_in) * p.map_out + p.map_off + (my_m % p.map_in);
         else my_out = my_m;
       }
@@ -428,7 +432,7 @@ static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 extern "C" int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias, void* C,
                                 int64_t ldc, int64_t M, int64_t N, int64_t K, int act, const void* residual,
                                 int64_t ldr, int64_t res_mod, int64_t res_row_off, const int32_t* out_row_map,
-                                void* stream) {
+                                int64_t n_out_rows, void* stream) {
   if (M < 0 || N <= 0 || K <= 0 || M > INT32_MAX / 2 || N > INT32_MAX / 2 || K > INT32_MAX / 2) return MM_ERR_BAD_ARG;
   if (M == 0) return MM_OK;
   if (!A || !W || !C) return MM_ERR_BAD_ARG;
@@ -437,6 +441,7 @@ extern "C" int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64
   if (!aligned16(A) || !aligned16(W) || !aligned16(C) || !aligned16(bias) || !aligned16(residual))
     return MM_ERR_BAD_ARG;
   if (act < MM_ACT_NONE || act > MM_ACT_GELU_TANH) return MM_ERR_BAD_ARG;
+  if (out_row_map && n_out_rows <= 0) return MM_ERR_BAD_ARG;
   CUtensorMap tmA, tmB;
   int rc = make_tmap_2d(&tmA, A, M, K, lda, BM);
   if (rc != MM_OK) return rc;
@@ -447,6 +452,7 @@ extern "C" int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64
   p.bias = reinterpret_cast<const __nv_bfloat16*>(bias);
   p.residual = reinterpret_cast<const __nv_bfloat16*>(residual);
   p.out_row_map = out_row_map;
+  p.n_out_rows = out_row_map ? n_out_rows : M;
   p.ldc = ldc;
   p.ldr = ldr;
   p.M = (int)M, p.N = (int)N, p.K = (int)K;

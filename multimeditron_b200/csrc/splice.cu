@@ -372,6 +372,8 @@ extern "C" int mm_attach_positions(const int64_t* input_ids, int64_t n_ids, int6
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   int32_t* blk = reinterpret_cast<int32_t*>(workspace);
   const int nblk = (int)((n_ids + kScanChunk - 1) / kScanChunk);
+  // rows beyond the actual count stay -1 (= "skip") so a count mismatch can never scatter through garbage
+  if (dest_rows && n_rows_cap > 0) MM_CUDA_CHECK(cudaMemsetAsync(dest_rows, 0xFF, (size_t)n_rows_cap * 4, st));
   if (nblk > 0) {
     attach_count_kernel<<<nblk, kScanThreads, 0, st>>>(input_ids, n_ids, attachment_id, blk);
     MM_CUDA_CHECK(cudaGetLastError());

@@ -229,10 +229,11 @@ def gemm_bias_act(a: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = 
     assert out.dtype == torch.bfloat16 and out.stride(-1) == 1
     ldc = out.stride(-2) if out.dim() >= 2 else N
     ldr = residual.stride(-2) if residual is not None else 0
+    n_out_rows = (out.numel() // N if out.is_contiguous() else out.shape[0]) if out_row_map is not None else 0
     with _timed("mm_gemm_bias_act", 2.0 * M * N * K):
         rc = lib.mm_gemm_bias_act(_ptr(a), a.stride(0), _ptr(w), w.stride(0), _ptr(bias), _ptr(out), ldc, M, N, K,
                               int(act), _ptr(residual), ldr, int(res_mod), int(res_row_off), _ptr(out_row_map),
-                              _stream())
+                                  n_out_rows, _stream())
     _check(rc, "mm_gemm_bias_act")
     return out
 

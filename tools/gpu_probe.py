@@ -198,10 +198,35 @@ def probe_tower():
         report(f"tower {name}", y.reshape(-1, H).cpu(), ref.reshape(-1, H), tol=3e-2)
 
 
+def probe_gemmshapes():
+    """Per-shape throughput of the GEMMs of one CLIP-L/14-336 step (M = 256*577)."""
+    M = 256 * 577
+    shapes = [("qkv", 3072, 1024, 0, False), ("out", 1024, 1024, 0, True), ("fc1", 4096, 1024, 1, False),
+              ("fc2", 1024, 4096, 0, True), ("fc1-noact", 4096, 1024, 0, False), ("out-nores", 1024, 1024, 0, False),
+              ("proj0", 1024, 1024, 2, False), ("proj2", 4096, 1024, 2, False), ("proj4", 4096, 4096, 0, False)]
+    for name, N, K, act, res in shapes:
+        a = torch.randn(M, K, device=dev).bfloat16()
+        w = (torch.randn(N, K, device=dev) * 0.02).bfloat16()
+        b = torch.randn(N, device=dev).bfloat16()
+        r = torch.randn(M, N, device=dev).bfloat16() if res else None
+        out = torch.empty(M, N, device=dev).bfloat16()
+        for _ in range(2):
+            ops.gemm_bias_act(a, w, b, act, residual=r, out=out)
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record()
+        for _ in range(5):
+            ops.gemm_bias_act(a, w, b, act, residual=r, out=out)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 5
+        print(f"{name:10s} M{M} N{N} K{K} act{act} res{int(res)}: {ms:.3f} ms {2 * M * N * K / ms / 1e9:.0f} TFLOP/s", flush=True)
+        del a, w, r, out
+
+
 if __name__ == "__main__":
     which = sys.argv[1]
     t = time.time()
     {"splice": probe_splice, "ln": probe_ln, "gemm": probe_gemm, "patch": probe_patch, "attn": probe_attn,
-     "tower": probe_tower}[which]()
+     "tower": probe_tower, "gemmshapes": probe_gemmshapes}[which]()
     torch.cuda.synchronize()
     print(f"-- {which} done in {time.time() - t:.1f}s", flush=True)
