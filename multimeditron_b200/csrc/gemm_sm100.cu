@@ -9,8 +9,9 @@
 //   * second instantiation (kGatherA): the A operand is gathered straight from NCHW pixels by four
 //     producer warps (im2col-free implicit GEMM of the patch convolution).
 //
-// Warp roles (TMA variant, 256 threads): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator,
-// w4..w7 epilogue (TMEM lane quadrant = warp % 4).  Gather variant adds w8..w11 = A producers.
+// Warp roles (TMA variant, 384 threads): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator,
+// w4..w11 epilogue (TMEM lane quadrant = warp % 4; two warps per quadrant split the 256 columns).
+// Gather variant (384 threads): w4..w7 epilogue, w8..w11 = A producers.
 //
 // Reference call sites replaced: see include/mm_b200.h (mm_gemm_bias_act, mm_patch_embed).
 #include "common.cuh"
@@ -20,26 +21,36 @@ namespace mm {
 constexpr int BM = 128;
 constexpr int BN = 256;
 constexpr int BK = 64;  // 64 bf16 = 128 B = one SWIZZLE_128B row
-constexpr int kStages = 4;
 constexpr int kUmmaK = 16;
 constexpr int kAStageBytes = BM * BK * 2;  // 16 KiB
 constexpr int kBStageBytes = BN * BK * 2;  // 32 KiB
 constexpr int kEpiWarpBytes = 32 * 128;    // 32 rows x 64 bf16
-constexpr int kEpiBytes = 4 * kEpiWarpBytes;
 constexpr int kTmemCols = 512;
 constexpr int kKTableMax = 3072 + 64;  // patch-embed k -> pixel offset table (ints)
 
+constexpr int kMaxStages = 4;
 struct GemmSmemTail {
-  uint64_t full[kStages];
-  uint64_t empty[kStages];
+  uint64_t full[kMaxStages];
+  uint64_t empty[kMaxStages];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
   uint32_t tmem_base;
 };
 
-constexpr int kGemmSmemBytes = 1024 /*align slack*/ + kStages * (kAStageBytes + kBStageBytes) + kEpiBytes + 256;
+// TMA variant: 4 stages, 8 epilogue warps (2 per TMEM lane quadrant, each owning half of the 256 columns).
+// Gather variant (patch embed): 3 stages, 4 epilogue warps, 4 A-producer warps, + 12.5 KiB static k-offset table.
+template <bool kGatherA>
+struct GemmCfg {
+  static constexpr int kStages = kGatherA ? 3 : 4;
+  static constexpr int kEpiWarps = kGatherA ? 4 : 8;
+  static constexpr int kChunksPerWarp = (BN / 64) / (kEpiWarps / 4);
+  static constexpr int kThreads = 128 + kEpiWarps * 32 + (kGatherA ? 128 : 0);
+  static constexpr int kEpiBytes = kEpiWarps * kEpiWarpBytes;
+  static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * (kAStageBytes + kBStageBytes) + kEpiBytes + 256;
+};
 static_assert(sizeof(GemmSmemTail) <= 256, "tail too large");
-static_assert(kGemmSmemBytes <= 232448, "smem budget");
+static_assert(GemmCfg<false>::kSmemBytes <= 232448, "smem budget");
+static_assert(GemmCfg<true>::kSmemBytes + kKTableMax * 4 <= 232448, "smem budget (gather)");
 
 struct GemmParams {
   __nv_bfloat16* C;
@@ -60,31 +71,53 @@ struct GemmParams {
   int k_real;            // 3*patch*patch
 };
 
-__device__ __forceinline__ float apply_act(float x, int act) {
-  switch (act) {
-    case MM_ACT_QUICK_GELU:
-      return x * __fdividef(1.0f, 1.0f + __expf(-1.702f * x));
-    case MM_ACT_GELU_ERF:
-      return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
-    case MM_ACT_GELU_TANH: {
-      float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
-      return 0.5f * x * (1.0f + tanhf(u));
-    }
-    default:
-      return x;
+__device__ __forceinline__ float fast_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fast_rcp(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// x * sigmoid(k*x) with one ex2 and one rcp (MUFU), k folded with log2(e)
+__device__ __forceinline__ float x_sigmoid(float x, float k_log2e) { return x * fast_rcp(1.0f + fast_ex2(-k_log2e * x)); }
+
+template <int ACT>
+__device__ __forceinline__ float apply_act(float x) {
+  if (ACT == MM_ACT_QUICK_GELU) {  // x * sigmoid(1.702 x)
+    return x_sigmoid(x, 1.702f * 1.4426950408889634f);
+  } else if (ACT == MM_ACT_GELU_TANH) {  // 0.5x(1+tanh(u)) == x*sigmoid(2u), u = sqrt(2/pi)(x + 0.044715x^3)
+    const float u2 = x * (1.5957691216057308f + 0.07135481282636213f * x * x);  // 2u
+    return x * fast_rcp(1.0f + fast_ex2(-1.4426950408889634f * u2));
+  } else if (ACT == MM_ACT_GELU_ERF) {  // exact GELU; erf by Abramowitz-Stegun 7.1.26 (|err| <= 1.5e-7)
+    const float ax = fabsf(x) * 0.70710678118654752440f;
+    const float t = fast_rcp(fmaf(0.3275911f, ax, 1.0f));
+    float poly = fmaf(t, 1.061405429f, -1.453152027f);
+    poly = fmaf(poly, t, 1.421413741f);
+    poly = fmaf(poly, t, -0.284496736f);
+    poly = fmaf(poly, t, 0.254829592f);
+    poly *= t;
+    const float erf_abs = 1.0f - poly * fast_ex2(-1.4426950408889634f * ax * ax);
+    return 0.5f * x * (1.0f + copysignf(erf_abs, x));
   }
+  return x;
 }
 
-template <bool kGatherA>
-__global__ void __launch_bounds__(kGatherA ? 384 : 256, 1)
+template <bool kGatherA, int ACT>
+__global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
     gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                         const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  using Cfg = GemmCfg<kGatherA>;
+  constexpr int kStages = Cfg::kStages;
+  constexpr int kEpiWarps = Cfg::kEpiWarps;
   uint8_t* sA = smem;
   uint8_t* sB = smem + kStages * kAStageBytes;
   uint8_t* sEpi = sB + kStages * kBStageBytes;
-  GemmSmemTail* tail = reinterpret_cast<GemmSmemTail*>(sEpi + kEpiBytes);
+  GemmSmemTail* tail = reinterpret_cast<GemmSmemTail*>(sEpi + Cfg::kEpiBytes);
   __shared__ int s_koff[kGatherA ? kKTableMax : 1];
 
   const int warp = threadIdx.x >> 5;
@@ -103,7 +136,7 @@ __global__ void __launch_bounds__(kGatherA ? 384 : 256, 1)
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tail->tmem_full[i], 1);
-      mbar_init(&tail->tmem_empty[i], 4);
+      mbar_init(&tail->tmem_empty[i], kEpiWarps);
     }
     fence_barrier_init();
   }
@@ -188,11 +221,11 @@ __global__ void __launch_bounds__(kGatherA ? 384 : 256, 1)
         }
       }
     }
-  } else if (warp >= 4 && warp < 8) {
+  } else if (warp >= 4 && warp < 4 + kEpiWarps) {
     // =========================== epilogue ===========================
-    const int q = warp & 3;  // TMEM lane quadrant
-    uint8_t* stg = sEpi + q * kEpiWarpBytes;
-    const uint32_t stg_addr = smem_u32(stg);
+    const int q = warp & 3;             // TMEM lane quadrant (hardware: warp % 4)
+    const int half = (warp - 4) >> 2;   // which group of column chunks this warp owns
+    uint8_t* stg = sEpi + (warp - 4) * kEpiWarpBytes;
     int as = 0;
     uint32_t aphase = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
@@ -204,72 +237,80 @@ __global__ void __launch_bounds__(kGatherA ? 384 : 256, 1)
         if (p.out_row_map) {
           my_out = p.out_row_map[my_m];
           if ((int64_t)my_out >= p.n_out_rows) my_out = -1;  // never write outside C
+        } else if (p.map_in > 0) {
+          my_out = (my_m / p.map_in) * p.map_out + p.map_off + (my_m % p.map_in);
+        } else {
+          my_out = my_m;
         }
-        else if (p.map_in > 0) my_out = (my_m / p.map_in) * p.map_out + p.map_off + (my_m % p.map_in);
-        else my_out = my_m;
       }
       mbar_wait(&tail->tmem_full[as], aphase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
 #pragma unroll 1
-      for (int c = 0; c < BN / 64; ++c) {
+      for (int cc = 0; cc < Cfg::kChunksPerWarp; ++cc) {
+        const int c = half * Cfg::kChunksPerWarp + cc;
         const int col0 = n0 + c * 64;
         if (col0 >= p.N) break;  // warp-uniform
         uint32_t acc[64];
         tmem_ld_32x32b_x32(t_row + c * 64, acc);
         tmem_ld_32x32b_x32(t_row + c * 64 + 32, acc + 32);
+        // while the TMEM loads are in flight: prefetch this chunk's bias and residual segments
+        int4 bv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          bv[j] = make_int4(0, 0, 0, 0);
+          if (p.bias && col0 + j * 8 < p.N) bv[j] = __ldg(reinterpret_cast<const int4*>(p.bias + col0 + j * 8));
+        }
+        const int ch = lane & 7;
+        const int col = col0 + ch * 8;
+        int out_rows[8];
+        int4 rv[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const int r = it * 4 + (lane >> 3);
+          out_rows[it] = __shfl_sync(0xffffffffu, my_out, r);
+          if (col >= p.N) out_rows[it] = -1;
+          rv[it] = make_int4(0, 0, 0, 0);
+          if (p.residual && out_rows[it] >= 0) {
+            const int gm = m0 + q * 32 + r;
+            const int64_t rr = (int64_t)((p.res_mod > 0 ? gm % p.res_mod : gm) + p.res_row_off);
+            rv[it] = __ldg(reinterpret_cast<const int4*>(p.residual + rr * p.ldr + col));
+          }
+        }
         tc_wait_ld();
         // bias + activation in fp32, on the bf16-rounded pre-activation (nn.Linear output rounding)
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          const int col = col0 + j * 8;
-          uint32_t bw[4] = {0, 0, 0, 0};
-          if (p.bias && col < p.N) {
-            int4 bv = __ldg(reinterpret_cast<const int4*>(p.bias + col));
-            bw[0] = bv.x, bw[1] = bv.y, bw[2] = bv.z, bw[3] = bv.w;
-          }
-          uint32_t o[4];
+          const uint32_t bw[4] = {(uint32_t)bv[j].x, (uint32_t)bv[j].y, (uint32_t)bv[j].z, (uint32_t)bv[j].w};
+          uint4 o;
+          uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             float x0 = __uint_as_float(acc[j * 8 + 2 * e]) + bf16_lo(bw[e]);
             float x1 = __uint_as_float(acc[j * 8 + 2 * e + 1]) + bf16_hi(bw[e]);
-            if (p.act != MM_ACT_NONE) {
-              uint32_t r = pack_bf16x2(x0, x1);
-              x0 = apply_act(bf16_lo(r), p.act);
-              x1 = apply_act(bf16_hi(r), p.act);
+            if (ACT != MM_ACT_NONE) {
+              const uint32_t r = pack_bf16x2(x0, x1);
+              x0 = apply_act<ACT>(bf16_lo(r));
+              x1 = apply_act<ACT>(bf16_hi(r));
             }
-            o[e] = pack_bf16x2(x0, x1);
+            ow[e] = pack_bf16x2(x0, x1);
           }
-          const uint32_t sa = stg_addr + lane * 128 + ((j ^ (lane & 7)) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(sa), "r"(o[0]), "r"(o[1]), "r"(o[2]),
-                       "r"(o[3])
-                       : "memory");
+          *reinterpret_cast<uint4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) = o;
         }
         __syncwarp();
         // coalesced phase: 8 lanes cover one 128-B row segment, 4 rows per instruction
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
           const int r = it * 4 + (lane >> 3);
-          const int ch = lane & 7;
-          const int out_row = __shfl_sync(0xffffffffu, my_out, r);
-          const int col = col0 + ch * 8;
-          uint32_t v[4];
-          const uint32_t la = stg_addr + r * 128 + ((ch ^ (r & 7)) << 4);
-          asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
-                       : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
-                       : "r"(la));
-          if (out_row >= 0 && col < p.N) {
+          uint4 v = *reinterpret_cast<const uint4*>(stg + r * 128 + ((ch ^ (r & 7)) << 4));
+          if (out_rows[it] >= 0) {
             if (p.residual) {
-              const int gm = m0 + q * 32 + r;
-              const int64_t rr = (int64_t)((p.res_mod > 0 ? gm % p.res_mod : gm) + p.res_row_off);
-              int4 rv = __ldg(reinterpret_cast<const int4*>(p.residual + rr * p.ldr + col));
-              const uint32_t rw[4] = {(uint32_t)rv.x, (uint32_t)rv.y, (uint32_t)rv.z, (uint32_t)rv.w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e)
-                v[e] = pack_bf16x2(bf16_lo(v[e]) + bf16_lo(rw[e]), bf16_hi(v[e]) + bf16_hi(rw[e]));
+              v.x = pack_bf16x2(bf16_lo(v.x) + bf16_lo((uint32_t)rv[it].x), bf16_hi(v.x) + bf16_hi((uint32_t)rv[it].x));
+              v.y = pack_bf16x2(bf16_lo(v.y) + bf16_lo((uint32_t)rv[it].y), bf16_hi(v.y) + bf16_hi((uint32_t)rv[it].y));
+              v.z = pack_bf16x2(bf16_lo(v.z) + bf16_lo((uint32_t)rv[it].z), bf16_hi(v.z) + bf16_hi((uint32_t)rv[it].z));
+              v.w = pack_bf16x2(bf16_lo(v.w) + bf16_lo((uint32_t)rv[it].w), bf16_hi(v.w) + bf16_hi((uint32_t)rv[it].w));
             }
-            int4 ov = make_int4((int)v[0], (int)v[1], (int)v[2], (int)v[3]);
-            *reinterpret_cast<int4*>(p.C + (int64_t)out_row * p.ldc + col) = ov;
+            *reinterpret_cast<uint4*>(p.C + (int64_t)out_rows[it] * p.ldc + col) = v;
           }
         }
         __syncwarp();
@@ -283,9 +324,9 @@ __global__ void __launch_bounds__(kGatherA ? 384 : 256, 1)
         aphase ^= 1;
       }
     }
-  } else if (kGatherA && warp >= 8) {
+  } else if (kGatherA && warp >= 4 + kEpiWarps) {
     // =========================== A producers: gather patches from NCHW pixels ===========================
-    const int row = threadIdx.x - 256;  // 0..127 : one A row (= one patch) per thread
+    const int row = threadIdx.x - (4 + kEpiWarps) * 32;  // 0..127 : one A row (= one patch) per thread
     const int P = p.grid * p.grid;
     const float* px32 = reinterpret_cast<const float*>(p.pixels);
     const __nv_bfloat16* px16 = reinterpret_cast<const __nv_bfloat16*>(p.pixels);
@@ -403,14 +444,15 @@ int make_tmap_3d(CUtensorMap* tm, const void* ptr, int64_t d0, int64_t d1, int64
   return MM_OK;
 }
 
-template <bool kGatherA>
-static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
+template <bool kGatherA, int ACT>
+static int launch_gemm_inst(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
+  using Cfg = GemmCfg<kGatherA>;
   static bool attr_set[64] = {false};
   int dev = 0;
   MM_CUDA_CHECK(cudaGetDevice(&dev));
   if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-    MM_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_tn_kernel<kGatherA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       kGemmSmemBytes));
+    MM_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_tn_kernel<kGatherA, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg::kSmemBytes));
     attr_set[dev] = true;
   }
   p.tiles_m = (p.M + BM - 1) / BM;
@@ -418,9 +460,19 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParam
   const int tiles = p.tiles_m * p.tiles_n;
   const int sms = sm_count();
   const int grid = tiles < sms ? tiles : sms;
-  gemm_bf16_tn_kernel<kGatherA><<<grid, kGatherA ? 384 : 256, kGemmSmemBytes, st>>>(tmA, tmB, p);
+  gemm_bf16_tn_kernel<kGatherA, ACT><<<grid, Cfg::kThreads, Cfg::kSmemBytes, st>>>(tmA, tmB, p);
   MM_CUDA_CHECK(cudaGetLastError());
   return MM_OK;
+}
+
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
+  switch (p.act) {
+    case MM_ACT_NONE: return launch_gemm_inst<false, MM_ACT_NONE>(tmA, tmB, p, st);
+    case MM_ACT_QUICK_GELU: return launch_gemm_inst<false, MM_ACT_QUICK_GELU>(tmA, tmB, p, st);
+    case MM_ACT_GELU_ERF: return launch_gemm_inst<false, MM_ACT_GELU_ERF>(tmA, tmB, p, st);
+    case MM_ACT_GELU_TANH: return launch_gemm_inst<false, MM_ACT_GELU_TANH>(tmA, tmB, p, st);
+  }
+  return MM_ERR_BAD_ARG;
 }
 
 }  // namespace mm
@@ -458,7 +510,7 @@ extern "C" int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64
   p.M = (int)M, p.N = (int)N, p.K = (int)K;
   p.res_mod = (int)res_mod, p.res_row_off = (int)res_row_off;
   p.act = act;
-  return launch_gemm<false>(tmA, tmB, p, reinterpret_cast<cudaStream_t>(stream));
+  return launch_gemm(tmA, tmB, p, reinterpret_cast<cudaStream_t>(stream));
 }
 
 extern "C" int mm_patch_embed(const void* pixels, int pixel_dtype, int64_t B, int64_t img, int64_t patch,
@@ -493,7 +545,7 @@ extern "C" int mm_patch_embed(const void* pixels, int pixel_dtype, int64_t B, in
   p.pixel_is_f32 = (pixel_dtype == MM_F32);
   p.img = (int)img, p.patch = (int)patch, p.grid = (int)G;
   p.k_real = (int)Kreal;
-  rc = launch_gemm<true>(tmB, tmB, p, st);
+  rc = launch_gemm_inst<true, MM_ACT_NONE>(tmB, tmB, p, st);
   if (rc != MM_OK) return rc;
   if (cls) {
     const int64_t n = B * D;

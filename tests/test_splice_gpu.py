@@ -68,7 +68,7 @@ def test_negative_indices_wrap_like_index_put():
     ref = emb.cpu().clone()
     src = torch.randn(4, H)
     bi = torch.tensor([0, -1, 2, -3])
-    tr = torch.tensor([-1, 0, -10, 5])
+    tr = torch.tensor([-1, 0, -9, 5])  # no duplicate targets (index_put_ with duplicates is undefined)
     ref[bi, tr] = src
     ops.splice_scatter_idx(emb, src.to(DEV), bi.to(DEV), tr.to(DEV))
     assert torch.equal(emb.cpu(), ref)
