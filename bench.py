@@ -48,6 +48,7 @@ class ClockSampler:
 
     def __init__(self, index: int):
         self.index, self.rows, self.proc = index, [], None
+        self.t0 = self.t1 = None   # wall-clock window of the timed region (samples outside it are dropped)
 
     def start(self):
         try:
@@ -61,7 +62,20 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def wait_first_sample(self, timeout=20.0):
+        """nvidia-smi start-up takes seconds and briefly serialises with kernel launches: keep it OUT of the timed
+        region by starting the sampler early and waiting for its first line."""
+        t = time.time()
+        while self.proc is not None and not self.rows and time.time() - t < timeout:
+            time.sleep(0.05)
+
+    def mark_begin(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
 
     def stop(self):
         if self.proc is None:
@@ -73,7 +87,8 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons, pw = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        rows = [r for (ts, r) in self.rows if self.t0 is None or (self.t0 <= ts <= (self.t1 or ts) + 0.15)]
+        for r in rows:
             try:
                 sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
                 for n, v in zip(names, r[3:7]):
@@ -160,6 +175,9 @@ def run_b200(args):
 
     rank, local_rank, world = sharding.env_rank_world()
     assert torch.cuda.is_available(), "bench.py (B200 arm) needs a CUDA device; there is no CPU fallback"
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
@@ -217,20 +235,22 @@ def run_b200(args):
     torch.cuda.synchronize()
     embedder.check()
 
-    sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
-        sampler.start()
+        sampler.wait_first_sample()
+        sampler.mark_begin()
     # ---- timed region (device-resident inputs), per-op CUDA events recorded on the launching stream
     ops.LAUNCHES = 0
     ops.profile_start()
     ms = timed(step_dev, args.steps)
     prof = ops.profile_stop()
     launches_per_step = ops.LAUNCHES // args.steps
-    clocks = sampler.stop() if sampler else None
     # ---- e2e region (host buffers)
     for _ in range(2):
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
+    if sampler:
+        sampler.mark_end()
+    clocks = sampler.stop() if sampler else None
     embedder.check()
     assert int(status_h.item()) == 0
 

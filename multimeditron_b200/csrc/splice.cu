@@ -189,7 +189,7 @@ template <>
 __device__ __forceinline__ __nv_bfloat16 cvt1<float, __nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
 
 constexpr int kMoveThreads = 256;
-constexpr int kMoveUnroll = 4;
+constexpr int kMoveUnroll = 8;
 
 // mode 0: scatter  dest[rows[k]] = src[k]          (k over n_rows)
 // mode 1: scatter with (batch_idx, token_range) int64 pairs
@@ -249,47 +249,58 @@ __device__ __forceinline__ bool resolve(const MoveArgs& a, int64_t u, const S*& 
   }
 }
 
+// One warp moves one 4-KiB segment (32 lanes x kMoveUnroll 16-B vectors) of one row per iteration: the row lookup
+// (index load, bounds check, 64-bit address math) is warp-uniform and amortised over the segment, and every lane
+// keeps kMoveUnroll independent 16-B loads in flight before the first store.
 template <int MODE, typename S, typename D>
 __global__ void __launch_bounds__(kMoveThreads) move_rows_kernel(MoveArgs a) {
-  const int64_t vpr = a.hidden >> 3;  // vecs per row
-  const int64_t total = a.n_units * vpr;
-  const int64_t stride = (int64_t)gridDim.x * kMoveThreads;
-  for (int64_t i0 = (int64_t)blockIdx.x * kMoveThreads + threadIdx.x; i0 < total; i0 += stride * kMoveUnroll) {
-    Vec8<S> vs[kMoveUnroll];
-    Vec8<D> vd[kMoveUnroll];
-    D* dptr[kMoveUnroll];
-    int kind[kMoveUnroll];  // 0 skip, 1 from src (S), 2 from table (D)
-#pragma unroll
-    for (int j = 0; j < kMoveUnroll; ++j) {
-      const int64_t i = i0 + j * stride;
-      kind[j] = 0;
-      if (i < total) {
-        const int64_t u = i / vpr, v = i - u * vpr;
-        const S* sp = nullptr;
-        D* dp = nullptr;
-        if (resolve<MODE, S, D>(a, u, sp, dp)) {
-          kind[j] = 1;
-          vs[j].load(sp + v * 8);
-          dptr[j] = dp + v * 8;
-        } else if (MODE >= 2) {
-          int64_t id = a.ids[u];
-          bool is_src = (MODE == 2) && (a.sop[u] >= 0);
-          if (!is_src) {
-            if (id < 0 || id >= a.vocab) {
-              if (a.status) atomicOr(a.status, MM_STATUS_INDEX_OOB);
-            } else {
-              kind[j] = 2;
-              vd[j].load(reinterpret_cast<const D*>(a.table) + id * a.hidden + v * 8);
-              dptr[j] = dp + v * 8;
-            }
-          }
+  const int lane = threadIdx.x & 31;
+  const int vpr = (int)(a.hidden >> 3);  // vecs per row
+  constexpr int kSegVecs = 32 * kMoveUnroll;
+  const int segs = (vpr + kSegVecs - 1) / kSegVecs;
+  const int64_t total = a.n_units * segs;
+  const int64_t nwarps = (int64_t)gridDim.x * (kMoveThreads / 32);
+  for (int64_t w = (int64_t)blockIdx.x * (kMoveThreads / 32) + (threadIdx.x >> 5); w < total; w += nwarps) {
+    const int64_t u = w / segs;
+    const int v0 = (int)(w - u * segs) * kSegVecs + lane;
+    const S* sp = nullptr;
+    D* dp = nullptr;
+    int kind = 0;  // 0 skip, 1 from src (S), 2 from table (D)
+    const D* tp = nullptr;
+    if (resolve<MODE, S, D>(a, u, sp, dp)) {
+      kind = 1;
+    } else if (MODE >= 2) {
+      const bool is_src = (MODE == 2) && (a.sop[u] >= 0);
+      if (!is_src) {
+        const int64_t id = a.ids[u];
+        if (id < 0 || id >= a.vocab) {
+          if (a.status && lane == 0) atomicOr(a.status, MM_STATUS_INDEX_OOB);
+        } else {
+          kind = 2;
+          tp = reinterpret_cast<const D*>(a.table) + id * a.hidden;
         }
       }
     }
+    if (kind == 1) {
+      Vec8<S> vs[kMoveUnroll];
 #pragma unroll
-    for (int j = 0; j < kMoveUnroll; ++j) {
-      if (kind[j] == 1) convert(vs[j], vd[j]);
-      if (kind[j] != 0) vd[j].store(dptr[j]);
+      for (int j = 0; j < kMoveUnroll; ++j)
+        if (v0 + j * 32 < vpr) vs[j].load(sp + (int64_t)(v0 + j * 32) * 8);
+#pragma unroll
+      for (int j = 0; j < kMoveUnroll; ++j)
+        if (v0 + j * 32 < vpr) {
+          Vec8<D> vd;
+          convert(vs[j], vd);
+          vd.store(dp + (int64_t)(v0 + j * 32) * 8);
+        }
+    } else if (kind == 2) {
+      Vec8<D> vd[kMoveUnroll];
+#pragma unroll
+      for (int j = 0; j < kMoveUnroll; ++j)
+        if (v0 + j * 32 < vpr) vd[j].load(tp + (int64_t)(v0 + j * 32) * 8);
+#pragma unroll
+      for (int j = 0; j < kMoveUnroll; ++j)
+        if (v0 + j * 32 < vpr) vd[j].store(dp + (int64_t)(v0 + j * 32) * 8);
     }
   }
 }
@@ -327,8 +338,10 @@ static int launch_move(const MoveArgs& a, cudaStream_t st) {
                    ((reinterpret_cast<uintptr_t>(a.table) & 15) == 0);
   const int sms = sm_count();
   if (vec) {
-    const int64_t total = a.n_units * (a.hidden >> 3);
-    int64_t need = (total + (int64_t)kMoveThreads * kMoveUnroll - 1) / ((int64_t)kMoveThreads * kMoveUnroll);
+    const int64_t vpr = a.hidden >> 3;
+    const int64_t segs = (vpr + 32 * kMoveUnroll - 1) / (32 * kMoveUnroll);
+    const int64_t total = a.n_units * segs;               // warp-iterations
+    int64_t need = (total + kMoveThreads / 32 - 1) / (kMoveThreads / 32);
     int64_t cap = (int64_t)sms * 8;  // 8 resident 256-thread CTAs per SM
     int grid = (int)(need < cap ? need : cap);
     move_rows_kernel<MODE, S, D><<<grid, kMoveThreads, 0, st>>>(a);
