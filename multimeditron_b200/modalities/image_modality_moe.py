@@ -1,0 +1,291 @@
+"""B200-native mixture-of-experts image modalities — drop-ins for
+  * `MOEImageModality`     (src/multimeditron/model/modalities/image_modality_moe.py:91-246,  "moe_meditron_clip")
+  * `MOEImageModalityPEP`  (src/multimeditron/model/modalities/image_modality_moe_pep.py:91-288, "moe_meditron_clip_pep")
+
+Reference behaviour reproduced:
+  * EVERY expert runs on EVERY image; top-k is computed by the gating network and discarded;
+  * `weighted_average`: shared-projector variant permutes the gating weights into expert order
+    (image_modality_moe.py:171-177); the PEP variant does NOT (image_modality_moe_pep.py:212-216);
+  * `sequence_append`: [B,E,P,*] flattened to [B,E*P,*] (:167-169 / :206-209);
+  * state-dict keys `experts.<i>.*` (HF CLIPVisionTransformer), `projector.projection.*` (shared) or
+    `projectors.<i>.projection.*` (PEP), `gating_network.resnet.*`.
+The expert towers, projectors and the fusion run on the sm_100a kernels.  The gating network (ResNet-50,
+moe/gating.py:73-89) is NOT on the north-star path: it is a caller-supplied callable
+`gating(pixels[B,3,h,w]) -> weights[B,E]` (a torch module on cuDNN, or precomputed weights); `cross_attn` fusion is
+out of scope for this round and raises.
+"""
+from __future__ import annotations
+
+from typing import Any, Callable, Dict, List, Optional, Sequence
+
+import torch
+
+from .. import ops
+from ..configs import TowerConfig
+from ..vit import ProjectorWeights, TowerRunner, TowerWeights
+from .base import AutoModality, BaseModality, BaseModalityConfig, BaseModalityProcessor
+from .constants import MODALITY_VALUE_KEY, NUM_EMBEDDINGS_KEY
+from .image_modality import resolve_tower
+
+
+class B200MOEImageConfig(BaseModalityConfig):
+    """Same fields as MOEImageConfig (image_modality_moe.py:11-52) / MOEImageConfigPEP."""
+
+    def __init__(self, hidden_size: int = 1024, use_bias_proj: bool = True, expert_clip_names: Sequence = (),
+                 image_processor="openai/clip-vit-large-patch14", gating_path: str = "", top_k_experts: int = 1,
+                 projection_type: str = "mlp", generalist_idx: int = -1, fusion_method: str = "weighted_average",
+                 cross_attn_heads: int = 8, gating_class_names: Optional[Sequence[str]] = None,
+                 expert_towers: Optional[Dict[str, Any]] = None, **kwargs):
+        super().__init__(modality_type="image", hidden_size=hidden_size, **kwargs)
+        self.use_bias_proj = use_bias_proj
+        self.expert_clip_names = list(expert_clip_names)
+        self.top_k_experts = top_k_experts
+        self.gating_path = gating_path
+        self.projection_type = projection_type
+        self.image_processor = image_processor
+        self.generalist_idx = generalist_idx
+        self.fusion_method = fusion_method
+        self.cross_attn_heads = cross_attn_heads
+        # GatingNetworkConfig.class_names (read at image_modality_moe.py:125); kept in the config here because the
+        # gating network itself is supplied by the caller
+        self.gating_class_names = list(gating_class_names) if gating_class_names else None
+        # optional offline shape table: expert name -> configs.TOWERS key / TowerConfig fields (instead of resolving
+        # the name through HF AutoConfig, which needs the checkpoint directory or the hub)
+        self.expert_towers = dict(expert_towers) if expert_towers else None
+
+
+class B200MOEImageConfigPEP(B200MOEImageConfig):
+    pass
+
+
+class B200MOEImageProcessor(BaseModalityProcessor):
+    """MOEImageProcessor.process (image_modality_moe.py:55-87): num_embeddings = P * top_k_experts for
+    `sequence_append`, P for `weighted_average` / `cross_attn`, ValueError otherwise."""
+
+    def __init__(self, config):
+        super().__init__(config)
+        self.tower = resolve_tower(config.image_processor)
+        self._num_patches_per_entry = self.tower.num_patches
+        self.top_k_experts = config.top_k_experts
+        self.fusion_method = config.fusion_method
+        self.image_processor = None
+        from ..configs import TOWERS
+        if isinstance(config.image_processor, str) and config.image_processor not in TOWERS:
+            from transformers import AutoImageProcessor
+            self.image_processor = AutoImageProcessor.from_pretrained(config.image_processor)
+
+    def process(self, modality: Dict[str, Any]) -> Dict[str, Any]:
+        out = modality.copy()
+        image = modality[MODALITY_VALUE_KEY]
+        if not torch.is_tensor(image):
+            if self.image_processor is None:
+                raise ValueError("PIL input needs a checkpoint directory with an image processor")
+            image = self.image_processor(images=image, return_tensors="pt")["pixel_values"][0]
+        out[MODALITY_VALUE_KEY] = image
+        if self.fusion_method == "sequence_append":
+            out[NUM_EMBEDDINGS_KEY] = self._num_patches_per_entry * self.top_k_experts
+        elif self.fusion_method in ("weighted_average", "cross_attn"):
+            out[NUM_EMBEDDINGS_KEY] = self._num_patches_per_entry
+        else:
+            raise ValueError(f"Unknown fusion_method: {self.fusion_method}")
+        return out
+
+
+class _B200MOEBase(BaseModality):
+    """Shared host logic of the two MoE modalities (expert loop, gating alignment, fusion dispatch)."""
+
+    config_class = B200MOEImageConfig
+    preprocessor_class = B200MOEImageProcessor
+    per_expert_projector = False   # PEP subclass sets True
+
+    def __init__(self, config, state_dict: Optional[dict] = None, device=None,
+                 gating: Optional[Callable[[torch.Tensor], torch.Tensor]] = None):
+        super().__init__(config)
+        self.expert_names: List = list(config.expert_clip_names)
+        assert len(self.expert_names) > 0, "config.expert_clip_names must be non-empty"
+        table = getattr(config, "expert_towers", None) or {}
+        self.towers: List[TowerConfig] = [resolve_tower(table.get(n, n) if isinstance(n, str) else n)
+                                          for n in self.expert_names]
+        t0 = self.towers[0]
+        for t in self.towers[1:]:
+            # image_modality_moe_pep.py:136-141 (and torch.stack at image_modality_moe.py:165 for the shared variant)
+            assert t.patch_size == t0.patch_size and t.image_size == t0.image_size, \
+                "sequence_append requires identical (image_size, patch_size) across experts."
+            if not self.per_expert_projector:
+                assert t.hidden_size == t0.hidden_size, "shared projector needs experts of one width"
+        self._num_patches_per_entry = t0.num_patches
+        self._native_embed_dim = t0.hidden_size
+        self.generalist_idx = config.generalist_idx
+        self.fusion_method = config.fusion_method
+        if self.fusion_method.replace("-", "_") == "cross_attn":
+            raise NotImplementedError("cross_attn fusion (model/attention.py:48-101) is SURVEY.md §8(f)#3 (next)")
+        if self.fusion_method not in ("weighted_average", "sequence_append"):
+            raise ValueError(f"Unsupported fusion_method: {self.fusion_method}")
+        # perm[class_idx] = expert_idx (image_modality_moe.py:125-138)
+        names = getattr(config, "gating_class_names", None) or []
+        if names:
+            idx = {str(n): i for i, n in enumerate(map(str, self.expert_names))}
+            try:
+                perm = [idx[str(n)] for n in names]
+            except KeyError as e:
+                raise ValueError(f"Gating class name {e} not found in expert_clip_names: {self.expert_names}")
+        else:
+            perm = list(range(len(self.towers)))
+        self._perm_list = perm
+        self._gating = gating
+        self._runners: List[TowerRunner] = []
+        self._projs: List[ProjectorWeights] = []
+        self._maps: Dict[Any, torch.Tensor] = {}
+        self._staging = None
+        if state_dict is not None:
+            self.load_reference_state_dict(state_dict, device or torch.device("cuda", torch.cuda.current_device()))
+
+    @property
+    def embedding_size(self) -> int:
+        # shared: experts' native width (image_modality_moe.py:114-115); PEP: post-projection width (:251-253)
+        return self.config.hidden_size if self.per_expert_projector else self._native_embed_dim
+
+    @property
+    def rows_per_entry(self) -> int:
+        """Embedding rows one image contributes to the sequence (E*P for sequence_append)."""
+        P = self._num_patches_per_entry
+        return P * len(self.towers) if self.fusion_method == "sequence_append" else P
+
+    # -- weights ------------------------------------------------------------------------------------------------
+    def load_reference_state_dict(self, sd: dict, device, gating=None):
+        dev = torch.device(device)
+        pools: Dict[TowerConfig, dict] = {}
+        self._runners = [TowerRunner(TowerWeights(t, sd, dev, vm_prefix=f"experts.{i}.", with_projector=False),
+                                     shared_ws=pools.setdefault(t, {})) for i, t in enumerate(self.towers)]
+        if self.per_expert_projector:
+            self._projs = [ProjectorWeights(sd, dev, f"projectors.{i}.") for i in range(len(self.towers))]
+        else:
+            self._projs = [ProjectorWeights(sd, dev, "projector.")]
+        self._device = dev
+        self._perm = torch.tensor(self._perm_list, dtype=torch.int32, device=dev)
+        if gating is not None:
+            self._gating = gating
+        return self
+
+    def set_gating(self, gating: Callable[[torch.Tensor], torch.Tensor]):
+        """gating(pixels [B,3,h,w] on the device) -> weights [B,E] (or the reference's (logits, topk, weights))."""
+        self._gating = gating
+        return self
+
+    # -- helpers ------------------------------------------------------------------------------------------------
+    def _stack(self, inputs) -> torch.Tensor:
+        if not self._runners:
+            raise RuntimeError("no weights loaded (call load_reference_state_dict)")
+        if torch.is_tensor(inputs):
+            return inputs.to(self._device, non_blocking=True)
+        inputs = list(inputs)
+        if inputs and inputs[0].is_cuda:
+            return torch.stack(inputs, 0)
+        return torch.stack(inputs, 0).pin_memory().to(self._device, non_blocking=True)
+
+    def _weights(self, px: torch.Tensor) -> torch.Tensor:
+        if self._gating is None:
+            raise RuntimeError("no gating network set: call set_gating(callable) "
+                               "(the ResNet-50 gate is not part of the B200 path, SURVEY.md §8(f)#3)")
+        w = self._gating(px)
+        if isinstance(w, (tuple, list)):
+            w = w[2]
+        E = len(self.towers)
+        if w.shape != (px.shape[0], E):
+            raise RuntimeError(f"gating returned weights of shape {tuple(w.shape)}, expected {(px.shape[0], E)}")
+        return w.to(device=self._device, dtype=torch.float32).contiguous()
+
+    def _append_map(self, B: int, e: int) -> torch.Tensor:
+        """compact row (b*P+p) of expert e -> row ((b*E+e)*P+p) of the [B,E,P,*] stack."""
+        key = (B, e)
+        m = self._maps.get(key)
+        if m is None:
+            if len(self._maps) > 64:
+                self._maps.clear()
+            E, P = len(self.towers), self._num_patches_per_entry
+            r = torch.arange(B * P, device=self._device, dtype=torch.int64)
+            m = (((r // P) * E + e) * P + r % P).to(torch.int32)
+            self._maps[key] = m
+        return m
+
+    # -- the plugin call ------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def forward(self, inputs) -> torch.Tensor:
+        """-> [B, P, H] (weighted_average) or [B, E*P, H] (sequence_append), bf16."""
+        px = self._stack(inputs)
+        B, E, P, H = px.shape[0], len(self.towers), self._num_patches_per_entry, self.config.hidden_size
+        n_out = P if self.fusion_method == "weighted_average" else E * P
+        out = torch.empty(B, n_out, H, dtype=torch.bfloat16, device=self._device)
+        self._run(px, out.view(-1, H), None)
+        return out
+
+    @torch.no_grad()
+    def forward_into(self, inputs, embedded_tokens: torch.Tensor, dest_rows: torch.Tensor) -> torch.Tensor:
+        """forward + splice: output row k lands in embedded_tokens.view(-1,H)[dest_rows[k]] (model.py:441-444)."""
+        px = self._stack(inputs)
+        self._run(px, embedded_tokens.view(-1, embedded_tokens.shape[-1]), dest_rows)
+        return embedded_tokens
+
+    def _run(self, px: torch.Tensor, out2d: torch.Tensor, dest_rows: Optional[torch.Tensor]):
+        raise NotImplementedError
+
+    # -- training-mode switches (interface parity; backward is not part of this round) ------------------------------
+    def freeze_modality_embedder(self):
+        self.modality_frozen = True
+
+    def unfreeze_modality_embedder(self):
+        raise NotImplementedError("ViT/gating backward on the B200 path is SURVEY.md §8(f)#2 (next)")
+
+    def unfreeze_projection(self):
+        raise NotImplementedError("projector backward on the B200 path is SURVEY.md §8(f)#2 (next)")
+
+
+@AutoModality.register("moe_meditron_clip_b200")
+class B200MOEImageModality(_B200MOEBase):
+    """Shared projector, fusion in the experts' feature space (image_modality_moe.py:152-210)."""
+    config_class = B200MOEImageConfig
+    preprocessor_class = B200MOEImageProcessor
+    per_expert_projector = False
+
+    def _run(self, px, out2d, dest_rows):
+        B, E, P = px.shape[0], len(self.towers), self._num_patches_per_entry
+        D = self._native_embed_dim
+        r0, proj = self._runners[0], self._projs[0]
+        if self.fusion_method == "weighted_average":
+            w = self._weights(px)                                                  # :156
+            stack = torch.empty(E, B * P, D, dtype=torch.bfloat16, device=self._device)
+            for e, r in enumerate(self._runners):                                  # :160-162 (every expert)
+                r.features(px, out=stack[e])
+            fused = ops.weighted_expert_sum(stack, w, self._perm, B, P)            # :171-177 (permuted weights)
+        else:                                                                      # sequence_append :167-169
+            fused = torch.empty(B * E * P, D, dtype=torch.bfloat16, device=self._device)
+            for e, r in enumerate(self._runners):
+                r.features(px, out=fused, out_row_map=self._append_map(B, e))
+        r0.project(fused, proj, out=out2d, out_row_map=dest_rows)                  # :207
+
+
+@AutoModality.register("moe_meditron_clip_pep_b200")
+class B200MOEImageModalityPEP(_B200MOEBase):
+    """One projector per expert, fusion in the LLM's space (image_modality_moe_pep.py:191-249)."""
+    config_class = B200MOEImageConfigPEP
+    preprocessor_class = B200MOEImageProcessor
+    per_expert_projector = True
+
+    def _run(self, px, out2d, dest_rows):
+        B, E, P, H = px.shape[0], len(self.towers), self._num_patches_per_entry, self.config.hidden_size
+        if self.fusion_method == "weighted_average":
+            w = self._weights(px)                                                  # :194
+            stack = torch.empty(E, B * P, H, dtype=torch.bfloat16, device=self._device)
+            for e, (r, pw) in enumerate(zip(self._runners, self._projs)):          # :198-203
+                r.project(r.features(px), pw, out=stack[e])
+            fused = ops.weighted_expert_sum(stack, w, None, B, P)                  # :212-216 (NO permutation)
+            if dest_rows is None:
+                out2d.copy_(fused)
+            else:
+                ops.splice_scatter(out2d, fused, dest_rows)
+        else:                                                                      # sequence_append :206-209
+            for e, (r, pw) in enumerate(zip(self._runners, self._projs)):
+                m = self._append_map(B, e)
+                if dest_rows is not None:
+                    m = dest_rows[m.long()].contiguous()
+                r.project(r.features(px), pw, out=out2d, out_row_map=m)

@@ -78,7 +78,7 @@ class B200MultiModalEmbedder(torch.nn.Module):
         for name, stack in stacks.items():
             modality = self._get_modality_by_name(name)
             if positions_from == "device":
-                n_rows = len(stack) * modality._num_patches_per_entry
+                n_rows = len(stack) * getattr(modality, "rows_per_entry", modality._num_patches_per_entry)
                 dest_rows, _, _ = ops.attach_positions(ids, self.attachment_token_idx, expected_rows=n_rows,
                                                        want_src_of_pos=False, status=st)
             else:

@@ -68,6 +68,21 @@ def make_modality_state_dict(cfg: TowerConfig, llm_hidden: int, seed: int = 0, d
     return _draw(tower_keys(cfg) + projector_keys(cfg.hidden_size, llm_hidden), gen, dtype, device)
 
 
+def make_moe_state_dict(towers, llm_hidden: int, per_expert_projector: bool, seed: int = 0, dtype=torch.float32,
+                        device="cpu"):
+    """State dict of a MoE modality (image_modality_moe.py / image_modality_moe_pep.py): `experts.<i>.*` holds the HF
+    CLIPVisionTransformer of expert i, `projector.*` (shared) or `projectors.<i>.*` (PEP) the MLP projectors."""
+    gen = torch.Generator().manual_seed(seed)
+    keys = []
+    for i, cfg in enumerate(towers):
+        keys += [(f"experts.{i}." + k[len(VM):], shape, kind) for k, shape, kind in tower_keys(cfg)]
+        if per_expert_projector:
+            keys += projector_keys(cfg.hidden_size, llm_hidden, prefix=f"projectors.{i}.")
+    if not per_expert_projector:
+        keys += projector_keys(towers[0].hidden_size, llm_hidden, prefix="projector.")
+    return _draw(keys, gen, dtype, device)
+
+
 def make_pixels(cfg: TowerConfig, batch: int, seed: int = 0, device="cpu"):
     """Post-normalisation CLIP pixels are ~N(0,1); fp32 like the processor output."""
     gen = torch.Generator().manual_seed(1000 + seed)

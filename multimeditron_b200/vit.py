@@ -81,10 +81,12 @@ class ProjectorWeights:
 class TowerRunner:
     """Runs the tower (and projector) for batches of images; activation workspaces are cached per batch size."""
 
-    def __init__(self, weights: TowerWeights):
+    def __init__(self, weights: TowerWeights, shared_ws: dict | None = None):
+        """shared_ws: a dict shared by several runners of the SAME tower shape (MoE experts run one after the other
+        on one stream, so they can reuse one set of activation buffers)."""
         self.w = weights
         self.cfg = weights.cfg
-        self._ws = {}
+        self._ws = shared_ws if shared_ws is not None else {}
 
     # -- workspaces ----------------------------------------------------------------------------------------
     def _workspace(self, B: int):
@@ -99,12 +101,16 @@ class TowerRunner:
                 t = m % c.num_tokens
                 ws["drop_cls"] = torch.where(t == 0, torch.full_like(m, -1),
                                              (m // c.num_tokens) * c.num_patches + t - 1).to(torch.int32)
-            self._ws = {B: ws}  # keep only the latest batch size resident
+            self._ws.clear()    # keep only the latest batch size resident
+            self._ws[B] = ws
         return ws
 
     # -- tower -----------------------------------------------------------------------------------------------
-    def features(self, pixels: torch.Tensor) -> torch.Tensor:
-        """pixels [B,3,img,img] (fp32 or bf16, CUDA) -> encoder features [B*P, D] bf16 (CLS dropped)."""
+    def features(self, pixels: torch.Tensor, out: torch.Tensor | None = None,
+                 out_row_map: torch.Tensor | None = None) -> torch.Tensor:
+        """pixels [B,3,img,img] (fp32 or bf16, CUDA) -> encoder features [B*P, D] bf16 (CLS dropped).
+        With (out, out_row_map): feature row (b*P+p) is written to out.view(-1,D)[out_row_map[b*P+p]] instead
+        (int32 map over the B*P compact rows; used by the MoE stacks)."""
         c, w = self.cfg, self.w
         if pixels.shape[-1] != c.image_size or pixels.shape[-2] != c.image_size:
             # same exception class / message as HF:models/clip/modeling_clip.py:204-207
@@ -113,6 +119,11 @@ class TowerRunner:
         B = pixels.shape[0]
         ws = self._workspace(B)
         x, h, qkv, attn, mlp, feats = ws["x"], ws["h"], ws["qkv"], ws["attn"], ws["mlp"], ws["feats"]
+        if out is not None:
+            assert out.dtype == torch.bfloat16 and out.is_contiguous() and out.shape[-1] == c.hidden_size
+            if out_row_map is None:
+                assert out.numel() == feats.numel()
+                feats = out.view(feats.shape)
         T, D, nh, hd = c.num_tokens, c.hidden_size, c.num_attention_heads, c.head_dim
         act = ops.ACT_BY_NAME[c.hidden_act]
         ops.patch_embed(pixels.contiguous(), w.patch_w, w.patch_b, w.pos, w.cls, c.patch_size, out=x.view(B, T, D))
@@ -129,12 +140,29 @@ class TowerRunner:
             last = i == n_layers - 1
             if last and c.has_cls:
                 # last fc2 writes the compact [B*P, D] feature matrix directly (CLS rows never stored)
-                ops.gemm_bias_act(mlp, L["w2"], L["b2"], residual=x, out=feats, out_row_map=ws["drop_cls"])
+                rmap, dst = ws["drop_cls"], feats
+                if out is not None and out_row_map is not None:   # compose: token row -> compact row -> caller's row
+                    rmap = self._compose(ws, out_row_map)
+                    dst = out.view(-1, D)
+                ops.gemm_bias_act(mlp, L["w2"], L["b2"], residual=x, out=dst, out_row_map=rmap)
             else:
                 ops.gemm_bias_act(mlp, L["w2"], L["b2"], residual=x, out=x)
         if not c.has_cls:
+            if out is not None and out_row_map is not None:
+                raise NotImplementedError("row-mapped feature output needs a CLS tower (MoE experts are CLIP)")
             ops.layernorm(x, w.post_ln[0], w.post_ln[1], c.layer_norm_eps, out=feats)
-        return feats
+        return out if (out is not None and out_row_map is not None) else feats
+
+    @staticmethod
+    def _compose(ws, out_row_map: torch.Tensor) -> torch.Tensor:
+        """token-row map = out_row_map[drop_cls[m]] (with -1 kept); cached per map tensor."""
+        key = ("compose", out_row_map.data_ptr(), out_row_map.numel())
+        m = ws.get(key)
+        if m is None:
+            dc = ws["drop_cls"].long()
+            m = torch.where(dc >= 0, out_row_map.long()[dc.clamp(min=0)], dc).to(torch.int32)
+            ws[key] = m
+        return m
 
     # -- projector ---------------------------------------------------------------------------------------------
     def project(self, feats: torch.Tensor, proj: "ProjectorWeights | None" = None, out: torch.Tensor | None = None,

@@ -187,6 +187,78 @@ def gen_splice(ref):
     np.savez_compressed(os.path.join(GOLD, "token_range.npz"), **tr_out)
 
 
+MOE_CASES = [  # name, per-expert projector, fusion, experts, hidden, batch, weight seed, pixel seed
+    ("moe_shared_avg", False, "weighted_average", 3, 64, 3, 21, 5),
+    ("moe_shared_append", False, "sequence_append", 3, 64, 2, 22, 6),
+    ("moe_pep_avg", True, "weighted_average", 3, 64, 3, 23, 7),
+    ("moe_pep_append", True, "sequence_append", 3, 64, 2, 24, 8),
+]
+MOE_CLASS_ORDER = [2, 0, 1]   # gating class c is expert MOE_CLASS_ORDER[c]  (non-identity on purpose)
+
+
+def save_tiny_clip(cfg):
+    from transformers import CLIPConfig, CLIPImageProcessor, CLIPModel
+    tmp = tempfile.mkdtemp(prefix="clip_ckpt_")
+    vc = dict(hidden_size=cfg.hidden_size, intermediate_size=cfg.intermediate_size,
+              num_hidden_layers=cfg.num_hidden_layers, num_attention_heads=cfg.num_attention_heads,
+              image_size=cfg.image_size, patch_size=cfg.patch_size, layer_norm_eps=cfg.layer_norm_eps,
+              hidden_act=cfg.hidden_act)
+    tc = dict(hidden_size=32, intermediate_size=64, num_hidden_layers=1, num_attention_heads=2, vocab_size=64,
+              max_position_embeddings=16)
+    CLIPModel(CLIPConfig(vision_config=vc, text_config=tc, projection_dim=32)).save_pretrained(tmp)
+    CLIPImageProcessor(size={"shortest_edge": cfg.image_size},
+                       crop_size={"height": cfg.image_size, "width": cfg.image_size}).save_pretrained(tmp)
+    return tmp
+
+
+@torch.no_grad()
+def gen_moe(ref):
+    """Reference MOEImageModality / MOEImageModalityPEP (all experts + gating-weighted fusion) on the `tiny` tower."""
+    from multimeditron.model.modalities.image_modality_moe import MOEImageConfig, MOEImageModality
+    from multimeditron.model.modalities.image_modality_moe_pep import MOEImageConfigPEP, MOEImageModalityPEP
+    from multimeditron.model.modalities.moe.gating import GatingNetwork, GatingNetworkConfig
+    cfg = TOWERS["tiny"]
+    for name, pep, fusion, E, hidden, batch, wseed, pseed in MOE_CASES:
+        dirs = [save_tiny_clip(cfg) for _ in range(E)]
+        gdir = tempfile.mkdtemp(prefix="gating_")
+        torch.manual_seed(wseed)
+        GatingNetwork(GatingNetworkConfig(num_classes=E, top_k=1, image_processor_path=dirs[0],
+                                          class_names=[dirs[i] for i in MOE_CLASS_ORDER])).save_pretrained(gdir)
+        Cfg, Mod = (MOEImageConfigPEP, MOEImageModalityPEP) if pep else (MOEImageConfig, MOEImageModality)
+        m = Mod(Cfg(hidden_size=hidden, expert_clip_names=dirs, image_processor=dirs[0], gating_path=gdir,
+                    top_k_experts=E if fusion == "sequence_append" else 1, fusion_method=fusion)).eval()
+        m = m.float()   # the MoE projectors are hard-defaulted to bf16 (projectors/mlp.py:16): cast BEFORE loading
+        sd32 = synth.make_moe_state_dict([cfg] * E, hidden, pep, seed=wseed)
+        missing, unexpected = m.load_state_dict(sd32, strict=False)
+        assert not unexpected, unexpected
+        assert all(k.startswith("gating_network.") for k in missing), missing
+        # a random-init ResNet-50 gates ~uniformly, which would hide the weight->expert alignment: spread the logits
+        m.gating_network.resnet.fc.bias.data = torch.tensor([1.5, -0.5, 0.25][:E]) + 0.1 * torch.arange(E)
+        pixels = synth.make_pixels(cfg, batch, seed=pseed)
+        inputs = [pixels[i] for i in range(batch)]
+        _, _, w32 = m.gating_network(pixels)
+        y32 = m(inputs)
+        perm = m._gating_to_expert_perm.tolist()
+        assert perm == MOE_CLASS_ORDER
+        o32 = vit_oracle.moe_modality_forward(sd32, [cfg] * E, inputs, w32, perm, fusion, pep)
+        assert torch.equal(y32, o32), f"{name}: oracle != reference (fp32)"
+        mb = m.to(torch.bfloat16)
+        _, _, wb = mb.gating_network(pixels.to(torch.bfloat16))
+        yb = mb([p.to(torch.bfloat16) for p in inputs])
+        sdb = {k: v.to(torch.bfloat16) for k, v in sd32.items()}
+        ob = vit_oracle.moe_modality_forward(sdb, [cfg] * E, [p.to(torch.bfloat16) for p in inputs], wb, perm, fusion, pep)
+        assert torch.equal(yb, ob), f"{name}: oracle != reference (bf16)"
+        # the reference's own bf16 error with the SAME gating weights as the fp32 run (isolates tower/projector rounding)
+        ob_w32 = vit_oracle.moe_modality_forward(sdb, [cfg] * E, [p.to(torch.bfloat16) for p in inputs],
+                                                 w32.to(torch.bfloat16), perm, fusion, pep)
+        err = (ob_w32.float() - y32).abs().max().item()
+        print(f"[{name}] out {tuple(y32.shape)} absmax {y32.abs().max():.4f} bf16-vs-fp32 maxabs {err:.3e} "
+              f"weights {w32[0].tolist()}")
+        np.savez_compressed(os.path.join(GOLD, f"{name}.npz"), pep=pep, fusion=fusion, experts=E, hidden=hidden,
+                            batch=batch, wseed=wseed, pseed=pseed, perm=np.array(perm), weights32=w32.numpy(),
+                            out_fp32=y32.numpy(), out_bf16_w32_bits=bf16_bits(ob_w32))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     torch.manual_seed(0)
@@ -194,6 +266,7 @@ def main():
     ref = ref_shim.import_reference()
     gen_splice(ref)
     gen_modality(ref)
+    gen_moe(ref)
     print("golden written to", GOLD)
 
 

@@ -24,26 +24,26 @@ def _act(name: str, x: torch.Tensor) -> torch.Tensor:
     raise ValueError(name)
 
 
-def vision_embeddings(sd, cfg, pixels: torch.Tensor) -> torch.Tensor:
+def vision_embeddings(sd, cfg, pixels: torch.Tensor, vm: str = VM) -> torch.Tensor:
     """HF:models/clip/modeling_clip.py:202-219 (CLIP) / models/siglip/modeling_siglip.py:157-187 (SigLIP)."""
-    w = sd[VM + "embeddings.patch_embedding.weight"]
+    w = sd[vm + "embeddings.patch_embedding.weight"]
     if pixels.shape[-1] != cfg.image_size or pixels.shape[-2] != cfg.image_size:
         raise ValueError(
             f"Input image size ({pixels.shape[-2]}*{pixels.shape[-1]}) doesn't match model "
             f"({cfg.image_size}*{cfg.image_size}).")
-    b = sd.get(VM + "embeddings.patch_embedding.bias") if cfg.conv_bias else None
+    b = sd.get(vm + "embeddings.patch_embedding.bias") if cfg.conv_bias else None
     x = F.conv2d(pixels.to(dtype=w.dtype), w, b, stride=cfg.patch_size)      # :208-209
     x = x.flatten(2).transpose(1, 2)                                         # :210
-    pos = sd[VM + "embeddings.position_embedding.weight"]
+    pos = sd[vm + "embeddings.position_embedding.weight"]
     if cfg.has_cls:
-        cls = sd[VM + "embeddings.class_embedding"].expand(x.shape[0], 1, -1)  # :212
+        cls = sd[vm + "embeddings.class_embedding"].expand(x.shape[0], 1, -1)  # :212
         x = torch.cat([cls, x], dim=1)                                          # :213
     return x + pos.unsqueeze(0)                                              # :217
 
 
-def encoder_layer(sd, cfg, i: int, x: torch.Tensor) -> torch.Tensor:
+def encoder_layer(sd, cfg, i: int, x: torch.Tensor, vm: str = VM) -> torch.Tensor:
     """HF:models/clip/modeling_clip.py:363-385 (layer), :300-336 (attention, SDPA), :347-351 (MLP)."""
-    L = f"{VM}encoder.layers.{i}."
+    L = f"{vm}encoder.layers.{i}."
     D, nh, hd = cfg.hidden_size, cfg.num_attention_heads, cfg.head_dim
     B, T, _ = x.shape
     res = x
@@ -67,21 +67,21 @@ def encoder_layer(sd, cfg, i: int, x: torch.Tensor) -> torch.Tensor:
     return res + h
 
 
-def vision_last_hidden_state(sd, cfg, pixels: torch.Tensor, taps: dict | None = None) -> torch.Tensor:
+def vision_last_hidden_state(sd, cfg, pixels: torch.Tensor, taps: dict | None = None, vm: str = VM) -> torch.Tensor:
     """CLIP: HF:models/clip/modeling_clip.py:667-692 — pre_layrnorm, L layers, last_hidden_state WITHOUT
     post_layernorm.  SigLIP: HF:models/siglip/modeling_siglip.py:604-625 — no pre-LN, post_layernorm on all tokens."""
     D = cfg.hidden_size
-    x = vision_embeddings(sd, cfg, pixels)
+    x = vision_embeddings(sd, cfg, pixels, vm)
     if taps is not None:
         taps["embeddings"] = x
     if cfg.kind == "clip":
-        x = F.layer_norm(x, (D,), sd[VM + "pre_layrnorm.weight"], sd[VM + "pre_layrnorm.bias"], cfg.layer_norm_eps)
+        x = F.layer_norm(x, (D,), sd[vm + "pre_layrnorm.weight"], sd[vm + "pre_layrnorm.bias"], cfg.layer_norm_eps)
     for i in range(cfg.num_hidden_layers):
-        x = encoder_layer(sd, cfg, i, x)
+        x = encoder_layer(sd, cfg, i, x, vm)
         if taps is not None and (i == 0 or i == cfg.num_hidden_layers - 1):
             taps[f"layer{i}"] = x
     if cfg.kind == "siglip":
-        x = F.layer_norm(x, (D,), sd[VM + "post_layernorm.weight"], sd[VM + "post_layernorm.bias"], cfg.layer_norm_eps)
+        x = F.layer_norm(x, (D,), sd[vm + "post_layernorm.weight"], sd[vm + "post_layernorm.bias"], cfg.layer_norm_eps)
     return x
 
 
@@ -114,3 +114,28 @@ def moe_weighted_average(expert_feats: torch.Tensor, weights: torch.Tensor, perm
     w = weights if perm is None else weights[:, perm]
     w = w.to(expert_feats.dtype).unsqueeze(-1).unsqueeze(-1)
     return (expert_feats * w).sum(dim=1)
+
+
+def moe_modality_forward(sd, towers, inputs, weights: torch.Tensor, perm, fusion_method: str,
+                         per_expert_projector: bool) -> torch.Tensor:
+    """image_modality_moe.py:152-210 (shared projector: weights permuted :171-175, projector after fusion :207) and
+    image_modality_moe_pep.py:191-249 (projector per expert :198-203, NO permutation :212-216).
+    `weights` [B,E] = the gating network's softmax output (moe/gating.py:85-87) — an input here."""
+    pixels = torch.stack(list(inputs), dim=0) if not torch.is_tensor(inputs) else inputs
+    outs = []
+    for i, cfg in enumerate(towers):
+        f = vision_last_hidden_state(sd, cfg, pixels, vm=f"experts.{i}.")[:, 1:, :]
+        if per_expert_projector:
+            f = mlp_projector(sd, f, prefix=f"projectors.{i}.")
+        outs.append(f)
+    stacked = torch.stack(outs, dim=1)                                   # [B,E,P,*]
+    if fusion_method == "sequence_append":
+        fused = torch.flatten(stacked, start_dim=1, end_dim=2)
+    elif fusion_method == "weighted_average":
+        w = weights
+        if not per_expert_projector:
+            w = w.index_select(dim=-1, index=torch.as_tensor(perm, dtype=torch.long))
+        fused = (stacked * w.unsqueeze(-1).unsqueeze(-1)).sum(dim=1)
+    else:
+        raise ValueError(f"Unsupported fusion_method: {fusion_method}")
+    return fused if per_expert_projector else mlp_projector(sd, fused, prefix="projector.")

@@ -110,3 +110,39 @@ def test_synth_sequences_structure():
         assert starts.numel() == 3
         for s in starts.tolist():
             assert (row[s + 1: s + 10] == 3).all() and row[s + 10] == 5
+
+
+def test_moe_plugin_contract_on_cpu():
+    """MoE modalities: registry names, processor num_embeddings rule (image_modality_moe.py:55-87), gating class-name
+    permutation (image_modality_moe.py:125-138) and error classes — no GPU needed."""
+    import pytest
+    import torch
+    from multimeditron_b200.modalities import AutoModality, B200MOEImageModality, B200MOEImageModalityPEP
+    names = ["a", "b", "c"]
+    base = {"hidden_size": 64, "expert_clip_names": names, "image_processor": "tiny",
+            "expert_towers": {n: "tiny" for n in names}}
+    cfg = AutoModality.config_from_dict({"model_type": "moe_meditron_clip_b200", **base,
+                                         "gating_class_names": ["c", "a", "b"]})
+    m = AutoModality.from_config(cfg)
+    assert isinstance(m, B200MOEImageModality) and m._perm_list == [2, 0, 1] and m.embedding_size == 128
+    cfgp = AutoModality.config_from_dict({"model_type": "moe_meditron_clip_pep_b200", **base})
+    mp = AutoModality.from_config(cfgp)
+    assert isinstance(mp, B200MOEImageModalityPEP) and mp._perm_list == [0, 1, 2] and mp.embedding_size == 64
+    proc = AutoModality.preprocessor_from_name("moe_meditron_clip_b200", cfg)
+    assert proc.process({"type": "image", "value": torch.zeros(3, 32, 32)})["num_embeddings"] == 16
+    cfg_app = AutoModality.config_from_dict({"model_type": "moe_meditron_clip_b200", **base,
+                                             "fusion_method": "sequence_append", "top_k_experts": 3})
+    assert AutoModality.preprocessor_from_name("moe_meditron_clip_b200", cfg_app).process(
+        {"type": "image", "value": torch.zeros(3, 32, 32)})["num_embeddings"] == 48
+    with pytest.raises(ValueError):   # gating class not among the experts (image_modality_moe.py:131-132)
+        AutoModality.from_config(AutoModality.config_from_dict(
+            {"model_type": "moe_meditron_clip_b200", **base, "gating_class_names": ["a", "b", "zzz"]}))
+    with pytest.raises(ValueError):   # unknown fusion (processor :86-87)
+        AutoModality.preprocessor_from_name("moe_meditron_clip_b200", AutoModality.config_from_dict(
+            {"model_type": "moe_meditron_clip_b200", **base, "fusion_method": "nope"})).process(
+            {"type": "image", "value": torch.zeros(3, 32, 32)})
+    with pytest.raises(AssertionError):  # no experts (:105)
+        AutoModality.from_config(AutoModality.config_from_dict(
+            {"model_type": "moe_meditron_clip_b200", "hidden_size": 64, "expert_clip_names": []}))
+    with pytest.raises(RuntimeError):    # no weights loaded -> loud failure, no fallback
+        m([torch.zeros(3, 32, 32)])

@@ -1,0 +1,81 @@
+"""-m gpu: MoE image modalities through the plugin mirror vs the goldens produced by the reference
+`MOEImageModality` / `MOEImageModalityPEP`.  Tolerance: max|Δ| vs the reference fp32 run <= 2 x the reference's own
+bf16 error + 1e-4·range, and <= 2e-2 of range."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from multimeditron_b200 import synth
+from multimeditron_b200.configs import TOWERS
+from multimeditron_b200.modalities import AutoModality
+from multimeditron_b200.model import B200MultiModalEmbedder
+from oracle import splice_oracle
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+MOE_NAMES = ["moe_shared_avg", "moe_shared_append", "moe_pep_avg", "moe_pep_append"]
+
+
+def _build(g):
+    cfg = TOWERS["tiny"]
+    E, hidden, pep = int(g["experts"]), int(g["hidden"]), bool(g["pep"])
+    names = [f"expert{i}" for i in range(E)]
+    perm = g["perm"].tolist()
+    mcfg = AutoModality.config_from_dict({
+        "model_type": "moe_meditron_clip_pep_b200" if pep else "moe_meditron_clip_b200", "hidden_size": hidden,
+        "expert_clip_names": names, "expert_towers": {n: "tiny" for n in names}, "image_processor": "tiny",
+        "fusion_method": str(g["fusion"]), "top_k_experts": E if str(g["fusion"]) == "sequence_append" else 1,
+        "gating_class_names": [names[i] for i in perm]})
+    sd = synth.make_moe_state_dict([cfg] * E, hidden, pep, seed=int(g["wseed"]))
+    w = torch.from_numpy(g["weights32"])
+    m = AutoModality.from_config(mcfg).load_reference_state_dict(sd, DEV, gating=lambda px: w.to(px.device))
+    return m, cfg
+
+
+@pytest.mark.parametrize("name", MOE_NAMES)
+def test_moe_forward_vs_reference_golden(golden_dir, name):
+    g = np.load(os.path.join(golden_dir, f"{name}.npz"))
+    m, cfg = _build(g)
+    batch = int(g["batch"])
+    px = synth.make_pixels(cfg, batch, seed=int(g["pseed"]))
+    y = m([px[i] for i in range(batch)])
+    ref32 = torch.from_numpy(g["out_fp32"])
+    refbf = torch.from_numpy(g["out_bf16_w32_bits"]).view(torch.bfloat16).float()
+    assert y.shape == ref32.shape and y.dtype == torch.bfloat16
+    scale = ref32.abs().max().item()
+    err = (y.float().cpu() - ref32).abs().max().item()
+    ref_err = (refbf - ref32).abs().max().item()
+    print(f"[{name}] max-abs {err:.3e} (reference bf16 run: {ref_err:.3e}), max-abs/absmax {err / scale:.3e}")
+    assert err <= 2.0 * ref_err + 1e-4 * scale
+    assert err / scale <= 2e-2
+
+
+@pytest.mark.parametrize("name", ["moe_shared_append", "moe_pep_avg"])
+def test_moe_splice_fused_equals_unfused(golden_dir, name):
+    """forward_into (splice fused into the modality) must be bit-identical to forward + splice_scatter."""
+    g = np.load(os.path.join(golden_dir, f"{name}.npz"))
+    m, cfg = _build(g)
+    B, H, V, S = int(g["batch"]), int(g["hidden"]), 300, 80
+    rows = m.rows_per_entry
+    att, start, end, pad = V - 4, V - 3, V - 2, V - 1
+    ids, _ = synth.make_sequences(B, S, 1, rows, V - 4, att, start, end, pad, seed=3, padding_side="left", min_len=S - 6)
+    px = synth.make_pixels(cfg, B, seed=int(g["pseed"]))
+    ranges = [splice_oracle.compute_token_range(ids[b].numpy(), [rows], att) for b in range(B)]
+    bidx, trng = splice_oracle.collator_indices(ranges)
+    pmi = {"stacked": {"image": [px[i] for i in range(B)]}, "batch_idx": {"image": torch.from_numpy(bidx)},
+           "token_range": {"image": torch.from_numpy(trng)}}
+    table = (torch.randn(V, H, generator=torch.Generator().manual_seed(1)) * 0.02).bfloat16().to(DEV)
+    outs = []
+    for fuse in (True, False):
+        for pos in ("device", "collator"):
+            e = B200MultiModalEmbedder(table, [m], att, fuse_splice=fuse)
+            outs.append(e(ids, pmi, positions_from=pos))
+            e.check()
+    for o in outs[1:]:
+        assert torch.equal(o, outs[0])
+    proj = m(pmi["stacked"]["image"]).cpu()
+    want = splice_oracle.embed_modalities_with_text(table.cpu(), ids, pmi["batch_idx"]["image"],
+                                                    pmi["token_range"]["image"], proj)
+    assert torch.equal(outs[0].cpu(), want)

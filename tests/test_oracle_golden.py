@@ -108,3 +108,28 @@ def test_c_oracle_agrees_with_numpy_oracle():
         torch.from_numpy(table), torch.from_numpy(ids), torch.from_numpy(d_np.astype(np.int64) // 33),
         torch.from_numpy(d_np.astype(np.int64) % 33), torch.from_numpy(src)).numpy().reshape(-1, 16)
     assert np.array_equal(out, want)
+
+
+MOE_NAMES = ["moe_shared_avg", "moe_shared_append", "moe_pep_avg", "moe_pep_append"]
+
+
+@pytest.mark.parametrize("name", MOE_NAMES)
+def test_moe_oracle_matches_reference_golden(golden_dir, name):
+    """MOEImageModality / MOEImageModalityPEP run by oracle/make_golden.py (all experts, gating-weighted fusion, the
+    PEP 'no permutation' quirk with a non-identity class order)."""
+    g = np.load(os.path.join(golden_dir, f"{name}.npz"))
+    cfg = TOWERS["tiny"]
+    E, hidden, batch, pep = int(g["experts"]), int(g["hidden"]), int(g["batch"]), bool(g["pep"])
+    sd = synth.make_moe_state_dict([cfg] * E, hidden, pep, seed=int(g["wseed"]))
+    px = synth.make_pixels(cfg, batch, seed=int(g["pseed"]))
+    perm = g["perm"].tolist()
+    assert perm != sorted(perm)
+    with torch.no_grad():
+        y = vit_oracle.moe_modality_forward(sd, [cfg] * E, px, torch.from_numpy(g["weights32"]), perm, str(g["fusion"]), pep)
+        ref = torch.from_numpy(g["out_fp32"])
+        assert y.shape == ref.shape
+        assert torch.allclose(y, ref, rtol=0, atol=2e-5 * ref.abs().max().item())
+        if str(g["fusion"]) == "weighted_average" and not pep:   # the alignment matters: identity must NOT match
+            wrong = vit_oracle.moe_modality_forward(sd, [cfg] * E, px, torch.from_numpy(g["weights32"]),
+                                                    list(range(E)), "weighted_average", pep)
+            assert not torch.allclose(wrong, ref, rtol=0, atol=1e-3 * ref.abs().max().item())
