@@ -159,10 +159,16 @@ int mm_patch_embed(const void* pixels, int pixel_dtype, int64_t B, int64_t img, 
 /*
  * mm_attention_fwd — non-causal softmax(Q·Kᵀ·scale)·V for every (image, head), no mask,
  * tcgen05 QKᵀ / PV with TMEM accumulators and an online softmax in registers.
- * Replaces HF:models/clip/modeling_clip.py:318-331 (SDPA, HF:integrations/sdpa_attention.py:40).
- *   qkv [B*T, 3*D] bf16, columns [q | k | v], head h occupies columns h*head_dim.. of each third;
- *   out [B*T, D] bf16.  head_dim must be 64.
+ * Replaces HF:models/clip/modeling_clip.py:318-331 and HF:models/siglip/modeling_siglip.py:285-300
+ * (SDPA, HF:integrations/sdpa_attention.py:40).
+ *   head_dim 64 (CLIP) or 72 (SigLIP so400m); T <= 1024.
+ *   hs = mm_attention_head_stride(head_dim) is the column slot of one head in the qkv buffer: 64 -> 64,
+ *   72 -> 80 (the 8 pad columns of every slot must be zeros: the fused QKV weight/bias is packed once, at
+ *   load time, with zero rows there, so the QKV GEMM itself writes them).
+ *   qkv [B*T, 3*heads*hs] bf16, columns [q | k | v], head h occupies columns h*hs.. of each third;
+ *   out [B*T, heads*head_dim] bf16 (compact: pad columns are not stored).
  */
+int64_t mm_attention_head_stride(int64_t head_dim); /* -1 when head_dim is not supported */
 int mm_attention_fwd(const void* qkv, void* out, int64_t B, int64_t T, int64_t heads,
                      int64_t head_dim, float scale, void* stream);
 

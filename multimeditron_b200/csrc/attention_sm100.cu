@@ -1,50 +1,91 @@
-// attention_sm100.cu — non-causal multi-head attention forward for ViT towers (head_dim 64, T <= 640).
+// attention_sm100.cu — non-causal multi-head attention forward for ViT towers (CLIP head_dim 64, SigLIP head_dim 72).
 //
-// One persistent CTA per SM; work unit = (image, head).  K and V of the unit (ceil(T/128) tiles each) are
-// TMA-loaded once and stay resident in shared memory.  The CTA walks the 128-row query tiles TWO AT A TIME
-// (two "streams", one softmax warpgroup each), so that one stream's MUFU-bound softmax overlaps the other
-// stream's tensor-core work:
-//   S = Q·Kᵀ      tcgen05.mma 128x128x16, SS form (both operands K-major SWIZZLE_128B smem), fp32 in TMEM
-//   P = softmax   one query row per thread straight out of TMEM (tcgen05.ld 32x32b); online max/sum in the
-//                 exp2 domain; the running max only moves when it grows by > 8 (log2 units), so the O
-//                 accumulator is rescaled rarely; P goes back to TMEM as packed bf16 (tcgen05.st)
-//   O += P·V      tcgen05.mma 128x64x16, TS form: A = P read from TMEM, B = V consumed MN-major directly from
+// One persistent CTA per SM; work unit = (image, head).  The CTA walks the unit's 128-row query tiles TWO AT A
+// TIME ("streams", one softmax warpgroup each) so that one stream's MUFU-bound softmax overlaps the other
+// stream's tensor-core work.  K/V tiles travel through a shared-memory ring; when the whole unit fits in the
+// ring (CLIP: T <= 6*128) it is loaded once per unit and reused by every query pair, otherwise (SigLIP, T=729)
+// it is streamed once per query pair (L2 hits).
+//   S = Q·Kᵀ      tcgen05.mma 128 x BKV x 16, SS form (K-major SWIZZLE_128B smem operands), fp32 in TMEM
+//   P = softmax   one query row per thread; the whole S row is pulled into registers with ONE pass of
+//                 tcgen05.ld, which frees the S accumulator for the next QKᵀ before any exp is computed;
+//                 online max/sum in the exp2 domain; the running max only moves when it grows by > 8 (log2
+//                 units), so the O accumulator is rescaled rarely; P goes back to TMEM as packed bf16
+//   O += P·V      tcgen05.mma 128 x HD x 16, TS form: A = P from TMEM, B = V consumed MN-major directly from
 //                 its [kv, head_dim] TMA tile (no transpose pass); fp32 in TMEM
-// TMEM map (512 columns): S0 0..127 | S1 128..255 | P0 256..319 | P1 320..383 | O0 384..447 | O1 448..511.
+// head_dim 72 runs as HD = 80: the fused QKV GEMM writes each head into an 80-column slot whose last 8 columns
+// are exact zeros (zero weight rows, packed at load time), the first 64 columns of a head travel as a
+// SWIZZLE_128B tile and columns 64..79 as a SWIZZLE_32B tile (one extra k-step for QKᵀ, one extra N=16 MMA
+// per k-step for PV); only the 72 real columns of O are stored.  BKV is 96 there so that TMEM holds
+// 2 x (S 96 + P 48 + O 80) = 448 columns.
+// TMEM map: S0 | S1 | P0 | P1 | O0 | O1 (hd64: 128,128,64,64,64,64 = 512 columns).
 //
-// Replaces HF:models/clip/modeling_clip.py:318-331 (SDPA; scale = head_dim**-0.5, no mask, dropout 0).
+// Replaces HF:models/clip/modeling_clip.py:318-331 and HF:models/siglip/modeling_siglip.py:285-300
+// (SDPA; scale = head_dim**-0.5, no mask, dropout 0).
 #include "common.cuh"
 
 namespace mm {
 
-int make_tmap_3d(CUtensorMap* tm, const void* ptr, int64_t d0, int64_t d1, int64_t d2, int64_t ld1, int64_t ld2,
-                 int box_rows);
-
-constexpr int kHD = 64;
 constexpr int kBQ = 128;
-constexpr int kBKV = 128;
-constexpr int kMaxKV = 5;                  // T <= 640
-constexpr int kTileBytes = 128 * kHD * 2;  // 16 KiB : [128 rows x 64 bf16]
 constexpr int kAttnThreads = 384;          // w0 TMA, w1 MMA, w2 TMEM alloc, w3 idle, w4-7 stream 0, w8-11 stream 1
 constexpr float kRescaleThreshold = 8.0f;  // log2 units: P <= 2^8, harmless in bf16/fp32
+constexpr int kMaxStages = 8;
+
+template <int HD, int BKV>
+struct AttnCfg {
+  static_assert(HD == 64 || HD == 80, "head slots of 64 or 80 columns");
+  static_assert(BKV % 32 == 0 && BKV <= 128, "kv tile");
+  static constexpr int kHDX = HD - 64;                          // extra columns (SWIZZLE_32B tile)
+  static constexpr int kQMain = kBQ * 128;                      // bytes: [128 x 64] bf16
+  static constexpr int kQX = kHDX ? kBQ * 32 : 0;               //        [128 x 16] bf16
+  static constexpr int kKMain = BKV * 128;
+  static constexpr int kKX = kHDX ? BKV * 32 : 0;
+  static constexpr int kStageBytes = 2 * (kKMain + kKX);        // K + V
+  static constexpr int kQBytes = 2 * (kQMain + kQX);            // two streams
+  static constexpr int kBarBytes = 512;
+  static constexpr int kStagesRaw = (232448 - 1024 - kBarBytes - kQBytes) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > kMaxStages ? kMaxStages : kStagesRaw;
+  static constexpr int kSmemBytes = 1024 + kQBytes + kStages * kStageBytes + kBarBytes;
+  // TMEM columns
+  static constexpr int kColS = 0;                 // + s*BKV
+  static constexpr int kColP = 2 * BKV;           // + s*BKV/2
+  static constexpr int kColO = 3 * BKV;           // + s*HD
+  static_assert(3 * BKV + 2 * HD <= 512, "TMEM budget");
+  static_assert(kStages >= 2, "ring");
+};
 
 struct AttnBars {
-  uint64_t kv_full[kMaxKV];
-  uint64_t kv_free;  // all MMAs of the unit retired -> K/V smem reusable
+  uint64_t kv_full[kMaxStages], kv_empty[kMaxStages];
   uint64_t q_full[2], q_empty[2];
   uint64_t s_full[2], s_empty[2];
   uint64_t p_full[2], pv_done[2];
   uint64_t o_empty[2];
   uint32_t tmem_base;
 };
-constexpr int kAttnSmemBytes = 1024 + kTileBytes * (2 + 2 * kMaxKV) + 256;
-static_assert(sizeof(AttnBars) <= 256, "bars");
-static_assert(kAttnSmemBytes <= 232448, "smem budget");
+static_assert(sizeof(AttnBars) <= 512, "bars");
+
+struct AttnMaps {
+  CUtensorMap q_main, kv_main, q_x, kv_x;
+};
 
 struct AttnParams {
-  __nv_bfloat16* out;  // [B*T, D]
-  int B, T, heads, D;
-  float scale_log2;  // scale * log2(e)
+  __nv_bfloat16* out;  // [B*T, ld_out]
+  int B, T, heads;
+  int Dp;              // heads * HD : width of each of the q | k | v sections of a qkv row
+  int hd_out;          // real head_dim (64 or 72)
+  int ld_out;          // heads * hd_out
+  float scale_log2;    // scale * log2(e)
+};
+
+struct RingPos {
+  int stage;
+  uint32_t phase;
+  template <int NS>
+  __device__ __forceinline__ void advance() {
+    if (++stage == NS) {
+      stage = 0;
+      phase ^= 1u;
+    }
+  }
 };
 
 __device__ __forceinline__ float ex2(float x) {
@@ -66,25 +107,39 @@ __device__ __forceinline__ void tc_mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, 
       : "memory");
 }
 
+template <int HD, int BKV>
 __global__ void __launch_bounds__(kAttnThreads, 1)
-    attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p) {
+    attention_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnParams p) {
+  using Cfg = AttnCfg<HD, BKV>;
+  constexpr int NS = Cfg::kStages;
+  constexpr int HDX = Cfg::kHDX;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sQ = smem;                   // 2 tiles (one per stream)
-  uint8_t* sK = sQ + 2 * kTileBytes;
-  uint8_t* sV = sK + kMaxKV * kTileBytes;
-  AttnBars* bars = reinterpret_cast<AttnBars*>(sV + kMaxKV * kTileBytes);
+  uint8_t* sQ = smem;                                  // [Q0 main][Q1 main][Q0 x][Q1 x]
+  uint8_t* sQX = sQ + 2 * Cfg::kQMain;
+  uint8_t* sKV = sQ + Cfg::kQBytes;                    // per stage: [K main][V main][K x][V x]
+  AttnBars* bars = reinterpret_cast<AttnBars*>(sKV + NS * Cfg::kStageBytes);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nkv = (p.T + kBKV - 1) / kBKV;
+  const int nkv = (p.T + BKV - 1) / BKV;
   const int nq = (p.T + kBQ - 1) / kBQ;
   const int npair = (nq + 1) >> 1;
   const int units = p.B * p.heads;
+  const bool resident = nkv <= NS;  // whole unit fits in the ring: load K/V once per unit
 
-  if (warp == 0 && lane == 0) tma_prefetch_desc(&tmQKV);
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&maps.q_main);
+    tma_prefetch_desc(&maps.kv_main);
+    if (HDX) {
+      tma_prefetch_desc(&maps.q_x);
+      tma_prefetch_desc(&maps.kv_x);
+    }
+  }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < kMaxKV; ++i) mbar_init(&bars->kv_full[i], 1);
-    mbar_init(&bars->kv_free, 1);
+    for (int i = 0; i < NS; ++i) {
+      mbar_init(&bars->kv_full[i], 1);
+      mbar_init(&bars->kv_empty[i], 1);
+    }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&bars->q_full[s], 1);
       mbar_init(&bars->q_empty[s], 1);
@@ -105,193 +160,237 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
 
+  // register re-split (launch: 384 x 168): the service warpgroup keeps 56, each softmax thread gets 224 so that a
+  // whole 128-column S row plus its packed P row stay in registers (128*56 + 256*224 = 64512 = 384*168)
+  // (the role code is nested inside the two branches so that ptxas allocates each region with its own budget)
+  if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
   if (warp == 0) {
     // =========================== TMA producer ===========================
     if (elect_one_sync()) {
-      uint32_t unit_i = 0;
+      RingPos rp{0, 0};
       uint32_t qi[2] = {0, 0};
       auto load_q = [&](int s, int qt, int h, int b) {
         mbar_wait(&bars->q_empty[s], (qi[s] & 1) ^ 1);
-        mbar_arrive_expect_tx(&bars->q_full[s], kTileBytes);
-        tma_load_3d(sQ + s * kTileBytes, &tmQKV, &bars->q_full[s], h * kHD, qt * kBQ, b);
+        mbar_arrive_expect_tx(&bars->q_full[s], Cfg::kQMain + Cfg::kQX);
+        tma_load_3d(sQ + s * Cfg::kQMain, &maps.q_main, &bars->q_full[s], h * HD, qt * kBQ, b);
+        if (HDX) tma_load_3d(sQX + s * Cfg::kQX, &maps.q_x, &bars->q_full[s], h * HD + 64, qt * kBQ, b);
         ++qi[s];
       };
-      for (int u = blockIdx.x; u < units; u += gridDim.x, ++unit_i) {
-        const int b = u / p.heads, h = u - b * p.heads;
-        mbar_wait(&bars->kv_free, (unit_i & 1) ^ 1);  // previous unit's MMAs done reading K/V
-        for (int kt = 0; kt < nkv; ++kt) {
-          mbar_arrive_expect_tx(&bars->kv_full[kt], 2 * kTileBytes);
-          tma_load_3d(sK + kt * kTileBytes, &tmQKV, &bars->kv_full[kt], p.D + h * kHD, kt * kBKV, b);
-          tma_load_3d(sV + kt * kTileBytes, &tmQKV, &bars->kv_full[kt], 2 * p.D + h * kHD, kt * kBKV, b);
-          if (kt == 0) {  // first pair of Q tiles right behind the first K/V tile so S(0) can start early
-            load_q(0, 0, h, b);
-            if (nq > 1) load_q(1, 1, h, b);
-          }
+      auto load_kv = [&](int kt, int h, int b) {
+        mbar_wait(&bars->kv_empty[rp.stage], rp.phase ^ 1);
+        uint64_t* full = &bars->kv_full[rp.stage];
+        uint8_t* st = sKV + rp.stage * Cfg::kStageBytes;
+        mbar_arrive_expect_tx(full, Cfg::kStageBytes);
+        tma_load_3d(st, &maps.kv_main, full, p.Dp + h * HD, kt * BKV, b);
+        tma_load_3d(st + Cfg::kKMain, &maps.kv_main, full, 2 * p.Dp + h * HD, kt * BKV, b);
+        if (HDX) {
+          tma_load_3d(st + 2 * Cfg::kKMain, &maps.kv_x, full, p.Dp + h * HD + 64, kt * BKV, b);
+          tma_load_3d(st + 2 * Cfg::kKMain + Cfg::kKX, &maps.kv_x, full, 2 * p.Dp + h * HD + 64, kt * BKV, b);
         }
-        for (int pi = 1; pi < npair; ++pi) {
-          load_q(0, 2 * pi, h, b);
-          if (2 * pi + 1 < nq) load_q(1, 2 * pi + 1, h, b);
+        rp.advance<NS>();
+      };
+      for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        const int b = u / p.heads, h = u - b * p.heads;
+        for (int pi = 0; pi < npair; ++pi) {
+          const bool two = 2 * pi + 1 < nq;
+          if (pi == 0 || !resident) {
+            for (int kt = 0; kt < nkv; ++kt) {
+              load_kv(kt, h, b);
+              if (kt == 0) {  // Q right behind the first K/V tile so S(0) can start early
+                load_q(0, 2 * pi, h, b);
+                if (two) load_q(1, 2 * pi + 1, h, b);
+              }
+            }
+          } else {
+            load_q(0, 2 * pi, h, b);
+            if (two) load_q(1, 2 * pi + 1, h, b);
+          }
         }
       }
     }
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
     if (elect_one_sync()) {
-      constexpr uint32_t idesc_s = umma_idesc_bf16(kBQ, kBKV, 0, 0);
-      constexpr uint32_t idesc_pv = umma_idesc_bf16(kBQ, kHD, 0, 1);  // B (= V) is MN-major
-      uint32_t unit_i = 0;
+      constexpr uint32_t idesc_s = umma_idesc_bf16(kBQ, BKV, 0, 0);
+      constexpr uint32_t idesc_pv = umma_idesc_bf16(kBQ, 64, 0, 1);   // B (= V) is MN-major
+      constexpr uint32_t idesc_pvx = umma_idesc_bf16(kBQ, 16, 0, 1);  // the 16 extra head columns
       uint32_t qi[2] = {0, 0}, it_s[2] = {0, 0}, it_pv[2] = {0, 0};
-      auto issue_s = [&](int s, int kt) {
+      RingPos cur{0, 0};
+      auto issue_s = [&](int s, int stage) {
         mbar_wait(&bars->s_empty[s], (it_s[s] & 1) ^ 1);
         tc_fence_after();
-        const uint32_t q_addr = smem_u32(sQ + s * kTileBytes);
-        const uint32_t k_addr = smem_u32(sK + kt * kTileBytes);
+        const uint32_t q_addr = smem_u32(sQ + s * Cfg::kQMain);
+        const uint32_t k_addr = smem_u32(sKV + stage * Cfg::kStageBytes);
+        const uint32_t d = tmem_base + Cfg::kColS + s * BKV;
 #pragma unroll
-        for (int k = 0; k < kHD / 16; ++k) {
-          tc_mma_f16_ss(tmem_base + s * 128, umma_desc_sw128(q_addr + k * 32, 16, 1024),
-                        umma_desc_sw128(k_addr + k * 32, 16, 1024), idesc_s, k != 0);
+        for (int k = 0; k < 4; ++k) {
+          tc_mma_f16_ss(d, umma_desc_sw128(q_addr + k * 32, 16, 1024), umma_desc_sw128(k_addr + k * 32, 16, 1024),
+                        idesc_s, k != 0);
+        }
+        if (HDX) {
+          const uint32_t qx = smem_u32(sQX + s * Cfg::kQX);
+          const uint32_t kx = smem_u32(sKV + stage * Cfg::kStageBytes + 2 * Cfg::kKMain);
+          tc_mma_f16_ss(d, umma_desc_sw32(qx, 16, 256), umma_desc_sw32(kx, 16, 256), idesc_s, 1);
         }
         tc_commit(&bars->s_full[s]);
         ++it_s[s];
       };
-      auto issue_pv = [&](int s, int kt) {
+      auto issue_pv = [&](int s, int kt, int stage) {
         mbar_wait(&bars->p_full[s], it_pv[s] & 1);
         if (kt == 0) mbar_wait(&bars->o_empty[s], (qi[s] & 1) ^ 1);  // previous tile's epilogue drained O
         tc_fence_after();
-        const uint32_t v_addr = smem_u32(sV + kt * kTileBytes);
+        const uint32_t v_addr = smem_u32(sKV + stage * Cfg::kStageBytes + Cfg::kKMain);
+        const uint32_t vx_addr = smem_u32(sKV + stage * Cfg::kStageBytes + 2 * Cfg::kKMain + Cfg::kKX);
+        const uint32_t d = tmem_base + Cfg::kColO + s * HD;
+        const uint32_t a = tmem_base + Cfg::kColP + s * (BKV / 2);
 #pragma unroll
-        for (int k = 0; k < kBKV / 16; ++k) {
-          // A = P from TMEM (16 bf16 = 8 columns per k-step); B = V MN-major, 16 kv rows = 2 KiB per k-step
-          tc_mma_f16_ts(tmem_base + 384 + s * 64, tmem_base + 256 + s * 64 + k * 8,
-                        umma_desc_sw128(v_addr + k * 2048, 1024, 1024), idesc_pv, (kt | k) != 0);
+        for (int k = 0; k < BKV / 16; ++k) {
+          // A = P from TMEM (16 bf16 = 8 columns per k-step); B = V MN-major, 16 kv rows per k-step
+          tc_mma_f16_ts(d, a + k * 8, umma_desc_sw128(v_addr + k * 2048, 1024, 1024), idesc_pv, (kt | k) != 0);
+          if (HDX)
+            tc_mma_f16_ts(d + 64, a + k * 8, umma_desc_sw32(vx_addr + k * 512, 256, 256), idesc_pvx, (kt | k) != 0);
         }
         tc_commit(&bars->pv_done[s]);
         ++it_pv[s];
       };
-      for (int u = blockIdx.x; u < units; u += gridDim.x, ++unit_i) {
+      for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        const RingPos ubase = cur;
         for (int pi = 0; pi < npair; ++pi) {
           const int ns = (2 * pi + 1 < nq) ? 2 : 1;  // active streams in this pair
+          const bool fresh = (pi == 0) || !resident;       // K/V tiles arrive during this pair
+          const bool release = (pi == npair - 1) || !resident;
+          RingPos st = resident ? ubase : cur;
+          int prev_stage = 0;
           for (int s = 0; s < ns; ++s) mbar_wait(&bars->q_full[s], qi[s] & 1);
           tc_fence_after();
           for (int kt = 0; kt < nkv; ++kt) {
-            if (pi == 0) mbar_wait(&bars->kv_full[kt], unit_i & 1);
+            if (fresh) mbar_wait(&bars->kv_full[st.stage], st.phase);
+            tc_fence_after();
             for (int s = 0; s < ns; ++s) {
-              issue_s(s, kt);
+              issue_s(s, st.stage);
               if (kt == nkv - 1) tc_commit(&bars->q_empty[s]);
             }
-            if (kt >= 1)
-              for (int s = 0; s < ns; ++s) issue_pv(s, kt - 1);
+            if (kt >= 1) {
+              for (int s = 0; s < ns; ++s) issue_pv(s, kt - 1, prev_stage);
+              if (release) tc_commit(&bars->kv_empty[prev_stage]);
+            }
+            prev_stage = st.stage;
+            st.advance<NS>();
           }
           for (int s = 0; s < ns; ++s) {
-            issue_pv(s, nkv - 1);
+            issue_pv(s, nkv - 1, prev_stage);
             ++qi[s];
           }
+          if (release) tc_commit(&bars->kv_empty[prev_stage]);
+          cur = st;
         }
-        tc_commit(&bars->kv_free);
       }
     }
-  } else if (warp >= 4) {
+  }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
     // =========================== softmax / correction / epilogue (stream = warpgroup) ===========================
+    constexpr int NCH = BKV / 32;
     const int s = (warp - 4) >> 2;
     const int q = warp & 3;
     const int row = q * 32 + lane;  // query row within the tile == TMEM lane
     const uint32_t lane_sel = (uint32_t)(q * 32) << 16;
-    const uint32_t t_S = tmem_base + s * 128 + lane_sel;
-    const uint32_t t_P = tmem_base + 256 + s * 64 + lane_sel;
-    const uint32_t t_O = tmem_base + 384 + s * 64 + lane_sel;
+    const uint32_t t_S = tmem_base + Cfg::kColS + s * BKV + lane_sel;
+    const uint32_t t_P = tmem_base + Cfg::kColP + s * (BKV / 2) + lane_sel;
+    const uint32_t t_O = tmem_base + Cfg::kColO + s * HD + lane_sel;
+    const float sl2 = p.scale_log2;
     uint32_t it = 0;
     for (int u = blockIdx.x; u < units; u += gridDim.x) {
       const int b = u / p.heads, h = u - b * p.heads;
       for (int qt = s; qt < nq; qt += 2) {
-        float m_run = -INFINITY, l_run = 0.f;  // running max (raw score units) and row sum
+        const bool warp_live = qt * kBQ + q * 32 < p.T;  // warps whose 32 rows are all padding only keep the protocol
+        float m_run = -INFINITY, l_run = 0.f;            // running max (raw score units) and row sum
         for (int kt = 0; kt < nkv; ++kt, ++it) {
-          const int valid = p.T - kt * kBKV;  // columns >= valid are padding (only in the last kv tile)
+          const int valid = p.T - kt * BKV;  // columns >= valid are padding (only in the last kv tile)
           mbar_wait(&bars->s_full[s], it & 1);
           tc_fence_after();
-          // ---- pass 1: row max
-          float mx = -INFINITY;
-#pragma unroll 1
-          for (int c = 0; c < kBKV / 32; ++c) {
-            if (c * 32 >= valid) break;
-            uint32_t sv[32];
-            tmem_ld_32x32b_x32(t_S + c * 32, sv);
+          uint32_t sv[BKV];
+          if (warp_live) {
+#pragma unroll
+            for (int c = 0; c < NCH; ++c)
+              if (c * 32 < valid) tmem_ld_32x32b_x32(t_S + c * 32, sv + c * 32);
             tc_wait_ld();
-            if (c * 32 + 32 <= valid) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(sv[j]));
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j)
-                if (c * 32 + j < valid) mx = fmaxf(mx, __uint_as_float(sv[j]));
-            }
           }
-          // the reference max only moves when it grows by more than the threshold (keeps O rescales rare)
-          float m_new = m_run;
-          if ((mx - m_run) * p.scale_log2 > kRescaleThreshold) m_new = mx;  // also true for m_run = -inf
-          const float m_scaled = m_new * p.scale_log2;
-          // ---- pass 2: p = exp2(s*scale - m*scale) -> packed bf16, row sum
-          uint32_t pk[kBKV / 2];
-          float sum = 0.f;
-#pragma unroll
-          for (int c = 0; c < kBKV / 32; ++c) {
-            if (c * 32 < valid) {
-              uint32_t sv[32];
-              tmem_ld_32x32b_x32(t_S + c * 32, sv);
-              tc_wait_ld();
-              if (c * 32 + 32 <= valid) {
-#pragma unroll
-                for (int j = 0; j < 32; j += 2) {
-                  const float p0 = ex2(fmaf(__uint_as_float(sv[j]), p.scale_log2, -m_scaled));
-                  const float p1 = ex2(fmaf(__uint_as_float(sv[j + 1]), p.scale_log2, -m_scaled));
-                  sum += p0 + p1;
-                  pk[c * 16 + (j >> 1)] = pack_bf16x2(p0, p1);
-                }
-              } else {
-#pragma unroll
-                for (int j = 0; j < 32; j += 2) {
-                  const float p0 =
-                      (c * 32 + j < valid) ? ex2(fmaf(__uint_as_float(sv[j]), p.scale_log2, -m_scaled)) : 0.f;
-                  const float p1 =
-                      (c * 32 + j + 1 < valid) ? ex2(fmaf(__uint_as_float(sv[j + 1]), p.scale_log2, -m_scaled)) : 0.f;
-                  sum += p0 + p1;
-                  pk[c * 16 + (j >> 1)] = pack_bf16x2(p0, p1);
-                }
-              }
-            } else {
-#pragma unroll
-              for (int j = 0; j < 16; ++j) pk[c * 16 + j] = 0u;
-            }
-          }
-          // S fully read -> the issuer may overwrite it with S(kt+1)
+          // the S accumulator now lives in registers: hand it back for the next QK^T right away
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&bars->s_empty[s]);
+          uint32_t pk[BKV / 2];
+          float m_new = m_run, sum = 0.f;
+          if (warp_live) {
+            if (valid < BKV) {
+#pragma unroll
+              for (int j = 0; j < BKV; ++j)
+                if (j >= valid) sv[j] = 0xff800000u;  // -inf
+            }
+            float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < BKV; j += 8) {
+              mx0 = fmaxf(mx0, fmaxf(__uint_as_float(sv[j + 0]), __uint_as_float(sv[j + 1])));
+              mx1 = fmaxf(mx1, fmaxf(__uint_as_float(sv[j + 2]), __uint_as_float(sv[j + 3])));
+              mx2 = fmaxf(mx2, fmaxf(__uint_as_float(sv[j + 4]), __uint_as_float(sv[j + 5])));
+              mx3 = fmaxf(mx3, fmaxf(__uint_as_float(sv[j + 6]), __uint_as_float(sv[j + 7])));
+            }
+            const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+            // the reference max only moves when it grows by more than the threshold (keeps O rescales rare)
+            if ((mx - m_run) * sl2 > kRescaleThreshold) m_new = mx;  // also true for m_run = -inf
+            const float m_scaled = m_new * sl2;
+            float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+              if (c * 32 < valid) {
+#pragma unroll
+                for (int j = c * 32; j < c * 32 + 32; j += 4) {
+                  const float p0 = ex2(fmaf(__uint_as_float(sv[j + 0]), sl2, -m_scaled));
+                  const float p1 = ex2(fmaf(__uint_as_float(sv[j + 1]), sl2, -m_scaled));
+                  const float p2 = ex2(fmaf(__uint_as_float(sv[j + 2]), sl2, -m_scaled));
+                  const float p3 = ex2(fmaf(__uint_as_float(sv[j + 3]), sl2, -m_scaled));
+                  sum0 += p0, sum1 += p1, sum2 += p2, sum3 += p3;
+                  pk[j >> 1] = pack_bf16x2(p0, p1);
+                  pk[(j >> 1) + 1] = pack_bf16x2(p2, p3);
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) pk[c * 16 + j] = 0u;
+              }
+            }
+            sum = (sum0 + sum1) + (sum2 + sum3);
+          }
           // P (TMEM) and the O accumulator are free once PV of the previous iteration retired
           if (it > 0) {
             mbar_wait(&bars->pv_done[s], (it - 1) & 1);
             tc_fence_after();
           }
-          if (kt > 0) {
-            const float alpha = ex2((m_run - m_new) * p.scale_log2);  // 1 when the max did not move
-            l_run = l_run * alpha + sum;
-            if (__any_sync(0xffffffffu, m_new != m_run)) {
+          if (warp_live) {
+            if (kt > 0) {
+              const float alpha = ex2((m_run - m_new) * sl2);  // 1 when the max did not move
+              l_run = l_run * alpha + sum;
+              if (__any_sync(0xffffffffu, m_new != m_run)) {
 #pragma unroll 1
-              for (int c = 0; c < kHD / 32; ++c) {
-                uint32_t o[32];
-                tmem_ld_32x32b_x32(t_O + c * 32, o);
-                tc_wait_ld();
+                for (int c = 0; c < HD / 16; ++c) {
+                  uint32_t o[16];
+                  tmem_ld_32x32b_x16(t_O + c * 16, o);
+                  tc_wait_ld();
 #pragma unroll
-                for (int j = 0; j < 32; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * alpha);
-                tmem_st_32x32b_x32(t_O + c * 32, o);
+                  for (int j = 0; j < 16; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * alpha);
+                  tmem_st_32x32b_x16(t_O + c * 16, o);
+                }
               }
+            } else {
+              l_run = sum;
             }
-          } else {
-            l_run = sum;
+            m_run = m_new;
+#pragma unroll
+            for (int c = 0; c < BKV / 64; ++c) tmem_st_32x32b_x32(t_P + c * 32, pk + c * 32);
+            if (BKV % 64) tmem_st_32x32b_x16(t_P + (BKV / 64) * 32, pk + (BKV / 64) * 32);
+            tc_wait_st();
           }
-          m_run = m_new;
-          tmem_st_32x32b_x32(t_P, pk);
-          tmem_st_32x32b_x32(t_P + 32, pk + 32);
-          tc_wait_st();
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&bars->p_full[s]);
@@ -299,23 +398,27 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         // ---- epilogue of the q tile: O / l -> bf16 -> global ----
         mbar_wait(&bars->pv_done[s], (it - 1) & 1);
         tc_fence_after();
-        const float inv_l = 1.0f / l_run;
-        const int t = qt * kBQ + row;
-        __nv_bfloat16* dst = p.out + ((int64_t)b * p.T + t) * p.D + h * kHD;
-#pragma unroll 1
-        for (int c = 0; c < kHD / 32; ++c) {
-          uint32_t o[32];
-          tmem_ld_32x32b_x32(t_O + c * 32, o);
-          tc_wait_ld();
-          if (t < p.T) {
+        if (warp_live) {
+          const float inv_l = 1.0f / l_run;
+          const int t = qt * kBQ + row;
+          __nv_bfloat16* dst = p.out + ((int64_t)b * p.T + t) * p.ld_out + h * p.hd_out;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              int4 v;
-              v.x = (int)pack_bf16x2(__uint_as_float(o[j * 8 + 0]) * inv_l, __uint_as_float(o[j * 8 + 1]) * inv_l);
-              v.y = (int)pack_bf16x2(__uint_as_float(o[j * 8 + 2]) * inv_l, __uint_as_float(o[j * 8 + 3]) * inv_l);
-              v.z = (int)pack_bf16x2(__uint_as_float(o[j * 8 + 4]) * inv_l, __uint_as_float(o[j * 8 + 5]) * inv_l);
-              v.w = (int)pack_bf16x2(__uint_as_float(o[j * 8 + 6]) * inv_l, __uint_as_float(o[j * 8 + 7]) * inv_l);
-              *reinterpret_cast<int4*>(dst + c * 32 + j * 8) = v;
+          for (int c = 0; c < HD / 16; ++c) {
+            uint32_t o[16];
+            tmem_ld_32x32b_x16(t_O + c * 16, o);
+            tc_wait_ld();
+            if (t < p.T) {
+#pragma unroll
+              for (int j = 0; j < 2; ++j) {
+                if (c * 16 + j * 8 < p.hd_out) {
+                  int4 v;
+                  v.x = (int)pack_bf16x2(__uint_as_float(o[j * 8 + 0]) * inv_l, __uint_as_float(o[j * 8 + 1]) * inv_l);
+                  v.y = (int)pack_bf16x2(__uint_as_float(o[j * 8 + 2]) * inv_l, __uint_as_float(o[j * 8 + 3]) * inv_l);
+                  v.z = (int)pack_bf16x2(__uint_as_float(o[j * 8 + 4]) * inv_l, __uint_as_float(o[j * 8 + 5]) * inv_l);
+                  v.w = (int)pack_bf16x2(__uint_as_float(o[j * 8 + 6]) * inv_l, __uint_as_float(o[j * 8 + 7]) * inv_l);
+                  *reinterpret_cast<int4*>(dst + c * 16 + j * 8) = v;
+                }
+              }
             }
           }
         }
@@ -336,37 +439,73 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
 
 }  // namespace mm
 
-using namespace mm;
+namespace mm {
+int make_tmap_3d(CUtensorMap* tm, const void* ptr, int64_t d0, int64_t d1, int64_t d2, int64_t ld1, int64_t ld2,
+                 int box_rows);
+int make_tmap_3d_sw32(CUtensorMap* tm, const void* ptr, int64_t d0, int64_t d1, int64_t d2, int64_t ld1, int64_t ld2,
+                      int box_rows);
 
-extern "C" int mm_attention_fwd(const void* qkv, void* out, int64_t B, int64_t T, int64_t heads, int64_t head_dim,
-                                float scale, void* stream) {
-  if (B < 0 || T <= 0 || heads <= 0) return MM_ERR_BAD_ARG;
-  if (head_dim != kHD || T > (int64_t)kMaxKV * kBKV) return MM_ERR_BAD_ARG;
-  if (B == 0) return MM_OK;
-  if (!qkv || !out || (reinterpret_cast<uintptr_t>(qkv) & 15) || (reinterpret_cast<uintptr_t>(out) & 15))
-    return MM_ERR_BAD_ARG;
-  if (B * heads > INT32_MAX / 2) return MM_ERR_BAD_ARG;
-  if (!(scale > 0.f)) return MM_ERR_BAD_ARG;  // the online max runs in raw-score units (needs scale > 0)
-  const int64_t D = heads * head_dim;
-  CUtensorMap tm;
-  int rc = make_tmap_3d(&tm, qkv, 3 * D, T, B, 3 * D, T * 3 * D, 128);
+template <int HD, int BKV>
+static int launch_attention(const void* qkv, const AttnParams& p, cudaStream_t st) {
+  using Cfg = AttnCfg<HD, BKV>;
+  AttnMaps maps;
+  const int64_t W = 3 * (int64_t)p.Dp;
+  int rc = make_tmap_3d(&maps.q_main, qkv, W, p.T, p.B, W, (int64_t)p.T * W, kBQ);
   if (rc != MM_OK) return rc;
+  rc = make_tmap_3d(&maps.kv_main, qkv, W, p.T, p.B, W, (int64_t)p.T * W, BKV);
+  if (rc != MM_OK) return rc;
+  if (Cfg::kHDX) {
+    rc = make_tmap_3d_sw32(&maps.q_x, qkv, W, p.T, p.B, W, (int64_t)p.T * W, kBQ);
+    if (rc != MM_OK) return rc;
+    rc = make_tmap_3d_sw32(&maps.kv_x, qkv, W, p.T, p.B, W, (int64_t)p.T * W, BKV);
+    if (rc != MM_OK) return rc;
+  } else {
+    maps.q_x = maps.q_main;
+    maps.kv_x = maps.kv_main;
+  }
   static bool attr_set[64] = {false};
   int dev = 0;
   MM_CUDA_CHECK(cudaGetDevice(&dev));
   if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-    MM_CUDA_CHECK(
-        cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmemBytes));
+    MM_CUDA_CHECK(cudaFuncSetAttribute(attention_fwd_kernel<HD, BKV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg::kSmemBytes));
     attr_set[dev] = true;
   }
-  AttnParams p;
-  p.out = reinterpret_cast<__nv_bfloat16*>(out);
-  p.B = (int)B, p.T = (int)T, p.heads = (int)heads, p.D = (int)D;
-  p.scale_log2 = scale * 1.4426950408889634f;
-  const int units = (int)(B * heads);
+  const int units = p.B * p.heads;
   const int sms = sm_count();
   const int grid = units < sms ? units : sms;
-  attention_fwd_kernel<<<grid, kAttnThreads, kAttnSmemBytes, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
+  attention_fwd_kernel<HD, BKV><<<grid, kAttnThreads, Cfg::kSmemBytes, st>>>(maps, p);
   MM_CUDA_CHECK(cudaGetLastError());
   return MM_OK;
+}
+}  // namespace mm
+
+using namespace mm;
+
+extern "C" int64_t mm_attention_head_stride(int64_t head_dim) {
+  if (head_dim == 64) return 64;
+  if (head_dim == 72) return 80;
+  return -1;
+}
+
+extern "C" int mm_attention_fwd(const void* qkv, void* out, int64_t B, int64_t T, int64_t heads, int64_t head_dim,
+                                float scale, void* stream) {
+  if (B < 0 || T <= 0 || heads <= 0) return MM_ERR_BAD_ARG;
+  const int64_t hs = mm_attention_head_stride(head_dim);
+  if (hs < 0 || T > 1024) return MM_ERR_BAD_ARG;
+  if (B == 0) return MM_OK;
+  if (!qkv || !out || (reinterpret_cast<uintptr_t>(qkv) & 15) || (reinterpret_cast<uintptr_t>(out) & 15))
+    return MM_ERR_BAD_ARG;
+  if (B * heads > INT32_MAX / 2 || B * T * 3 * heads * hs > ((int64_t)1 << 40)) return MM_ERR_BAD_ARG;
+  if (!(scale > 0.f)) return MM_ERR_BAD_ARG;  // the online max runs in raw-score units (needs scale > 0)
+  AttnParams p;
+  p.out = reinterpret_cast<__nv_bfloat16*>(out);
+  p.B = (int)B, p.T = (int)T, p.heads = (int)heads;
+  p.Dp = (int)(heads * hs);
+  p.hd_out = (int)head_dim;
+  p.ld_out = (int)(heads * head_dim);
+  p.scale_log2 = scale * 1.4426950408889634f;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (hs == 64) return launch_attention<64, 128>(qkv, p, st);
+  return launch_attention<80, 96>(qkv, p, st);
 }

@@ -444,6 +444,25 @@ int make_tmap_3d(CUtensorMap* tm, const void* ptr, int64_t d0, int64_t d1, int64
   return MM_OK;
 }
 
+// 3-D bf16 map with a [1, box_rows, 16]-element box, SWIZZLE_32B (the 16 extra head columns of head_dim 72)
+int make_tmap_3d_sw32(CUtensorMap* tm, const void* ptr, int64_t d0, int64_t d1, int64_t d2, int64_t ld1, int64_t ld2,
+                      int box_rows) {
+  PFN_encodeTiled enc = get_encode();
+  if (!enc) return MM_ERR_CUDA;
+  cuuint64_t gdim[3] = {(cuuint64_t)d0, (cuuint64_t)d1, (cuuint64_t)d2};
+  cuuint64_t gstr[2] = {(cuuint64_t)ld1 * 2, (cuuint64_t)ld2 * 2};
+  cuuint32_t box[3] = {16, (cuuint32_t)box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    g_last_cuda_error = 100000 + (int)r;
+    return MM_ERR_CUDA;
+  }
+  return MM_OK;
+}
+
 template <bool kGatherA, int ACT>
 static int launch_gemm_inst(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
   using Cfg = GemmCfg<kGatherA>;

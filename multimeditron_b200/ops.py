@@ -256,14 +256,25 @@ def patch_embed(pixels: torch.Tensor, weight_padded: torch.Tensor, conv_bias, po
     return out
 
 
+def attn_head_stride(head_dim: int) -> int:
+    """Column slot of one head in the qkv buffer (64 -> 64, 72 -> 80 with 8 zero pad columns)."""
+    hs = _lib.load().mm_attention_head_stride(head_dim)
+    if hs < 0:
+        raise MMError(f"mm_attention_fwd: head_dim {head_dim} is not supported (64 or 72)")
+    return int(hs)
+
+
 def attention_fwd(qkv: torch.Tensor, B: int, T: int, heads: int, head_dim: int, scale: float,
                   out: torch.Tensor | None = None) -> torch.Tensor:
+    """qkv [B*T, 3*heads*attn_head_stride(head_dim)] bf16 -> out [B*T, heads*head_dim] bf16."""
     _cuda(qkv)
     lib = _lib.load()
+    hs = attn_head_stride(head_dim)
     D = heads * head_dim
-    assert qkv.dtype == torch.bfloat16 and qkv.is_contiguous() and qkv.numel() == B * T * 3 * D
+    assert qkv.dtype == torch.bfloat16 and qkv.is_contiguous() and qkv.numel() == B * T * 3 * heads * hs
     if out is None:
         out = torch.empty(B * T, D, dtype=torch.bfloat16, device=qkv.device)
+    assert out.dtype == torch.bfloat16 and out.is_contiguous() and out.numel() == B * T * D
     with _timed("mm_attention_fwd", 4.0 * B * heads * T * T * head_dim):
         rc = lib.mm_attention_fwd(_ptr(qkv), _ptr(out), B, T, heads, head_dim, float(scale), _stream())
     _check(rc, "mm_attention_fwd")

@@ -48,15 +48,27 @@ class TowerWeights:
             self.post_ln = (_bf(sd[vm_prefix + "post_layernorm.weight"], dev),
                             _bf(sd[vm_prefix + "post_layernorm.bias"], dev))
         self.layers = []
+        nh, hd = cfg.num_attention_heads, cfg.head_dim
+        hs = ops.attn_head_stride(hd)   # head slot in the qkv buffer (72 -> 80: 8 zero rows per head)
+        self.head_stride = hs
+
+        def slot(t: torch.Tensor) -> torch.Tensor:
+            """[nh*hd, ...] -> [nh*hs, ...] with zero rows padding every head to its slot."""
+            if hs == hd:
+                return t
+            out = torch.zeros((nh, hs) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+            out[:, :hd] = t.view((nh, hd) + tuple(t.shape[1:]))
+            return out.view((nh * hs,) + tuple(t.shape[1:]))
+
         for i in range(cfg.num_hidden_layers):
             L = f"{vm_prefix}encoder.layers.{i}."
             g = lambda n: _bf(sd[L + n], dev)  # noqa: E731
             self.layers.append(dict(
                 ln1=(g("layer_norm1.weight"), g("layer_norm1.bias")),
-                wqkv=torch.cat([g("self_attn.q_proj.weight"), g("self_attn.k_proj.weight"),
-                                g("self_attn.v_proj.weight")], 0).contiguous(),
-                bqkv=torch.cat([g("self_attn.q_proj.bias"), g("self_attn.k_proj.bias"),
-                                g("self_attn.v_proj.bias")], 0).contiguous(),
+                wqkv=torch.cat([slot(g("self_attn.q_proj.weight")), slot(g("self_attn.k_proj.weight")),
+                                slot(g("self_attn.v_proj.weight"))], 0).contiguous(),
+                bqkv=torch.cat([slot(g("self_attn.q_proj.bias")), slot(g("self_attn.k_proj.bias")),
+                                slot(g("self_attn.v_proj.bias"))], 0).contiguous(),
                 wo=g("self_attn.out_proj.weight"), bo=g("self_attn.out_proj.bias"),
                 ln2=(g("layer_norm2.weight"), g("layer_norm2.bias")),
                 w1=g("mlp.fc1.weight"), b1=g("mlp.fc1.bias"),
@@ -95,7 +107,7 @@ class TowerRunner:
             c, dev = self.cfg, self.w.device
             M, D, I = B * c.num_tokens, c.hidden_size, c.intermediate_size
             e = lambda *s: torch.empty(*s, dtype=torch.bfloat16, device=dev)  # noqa: E731
-            ws = dict(x=e(M, D), h=e(M, D), qkv=e(M, 3 * D), attn=e(M, D), mlp=e(M, I), feats=e(B * c.num_patches, D))
+            ws = dict(x=e(M, D), h=e(M, D), qkv=e(M, 3 * c.num_attention_heads * self.w.head_stride), attn=e(M, D), mlp=e(M, I), feats=e(B * c.num_patches, D))
             if c.has_cls:  # GEMM row m (token) -> compact feature row, CLS rows dropped (image_modality.py:133)
                 m = torch.arange(M, device=dev, dtype=torch.int64)
                 t = m % c.num_tokens

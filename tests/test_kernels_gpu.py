@@ -129,22 +129,44 @@ def test_patch_embed(B, img, p, D, cls, bias, dt):
     close(out, ref + pos.float())
 
 
-@pytest.mark.parametrize("B,T,nh", [(1, 1, 1), (1, 50, 2), (2, 128, 2), (2, 129, 2), (2, 200, 3), (2, 577, 4), (3, 640, 2),
-                                    (40, 577, 16)])
-def test_attention_fwd(B, T, nh):
-    D = nh * 64
+@pytest.mark.parametrize("B,T,nh,hd", [
+    (1, 1, 1, 64), (1, 50, 2, 64), (2, 128, 2, 64), (2, 129, 2, 64), (2, 200, 3, 64), (2, 577, 4, 64), (3, 640, 2, 64),
+    (40, 577, 16, 64), (2, 769, 2, 64), (1, 1024, 3, 64),                       # > 6 kv tiles: streamed K/V ring
+    (1, 1, 1, 72), (2, 96, 2, 72), (2, 97, 2, 72), (3, 300, 3, 72), (2, 729, 16, 72), (20, 729, 16, 72),  # SigLIP
+    (1, 1000, 2, 72)])
+def test_attention_fwd(B, T, nh, hd):
+    hs = ops.attn_head_stride(hd)
     g0 = torch.Generator().manual_seed(B * T * nh)
-    qkv = (torch.randn(B * T, 3 * D, generator=g0) * 1.5).bfloat16().to(DEV)
-    out = ops.attention_fwd(qkv, B, T, nh, 64, 0.125)
-    q, k, v = [t.view(B, T, nh, 64).transpose(1, 2).float() for t in qkv.view(B, T, 3 * D).split(D, -1)]
-    ref = F.scaled_dot_product_attention(q, k, v, scale=0.125).transpose(1, 2).reshape(B * T, D)
+    qkv = torch.zeros(B * T, 3, nh, hs, dtype=torch.bfloat16)
+    qkv[..., :hd] = (torch.randn(B * T, 3, nh, hd, generator=g0) * 1.5).bfloat16()
+    qkv = qkv.view(B * T, 3 * nh * hs).to(DEV)
+    scale = hd ** -0.5
+    out = ops.attention_fwd(qkv, B, T, nh, hd, scale)
+    assert out.shape == (B * T, nh * hd)
+    x = qkv.view(B, T, 3, nh, hs)[..., :hd].float()
+    q, k, v = [x[:, :, i].transpose(1, 2) for i in range(3)]
+    ref = F.scaled_dot_product_attention(q, k, v, scale=scale).transpose(1, 2).reshape(B * T, nh * hd)
+    close(out, ref, tol=1e-2)
+
+
+def test_attention_peaked_rows_rescale():
+    """Scores whose running max jumps by far more than the lazy-rescale threshold between kv tiles."""
+    B, T, nh, hd = 1, 577, 2, 64
+    g0 = torch.Generator().manual_seed(5)
+    qkv = (torch.randn(B * T, 3, nh, hd, generator=g0)).bfloat16()
+    qkv[:, 1] *= torch.linspace(0.1, 12.0, T).view(T, 1, 1).bfloat16()   # later keys score much higher
+    qkv = qkv.view(B * T, 3 * nh * hd).to(DEV)
+    out = ops.attention_fwd(qkv, B, T, nh, hd, 0.125)
+    x = qkv.view(B, T, 3, nh, hd).float()
+    q, k, v = [x[:, :, i].transpose(1, 2) for i in range(3)]
+    ref = F.scaled_dot_product_attention(q, k, v, scale=0.125).transpose(1, 2).reshape(B * T, nh * hd)
     close(out, ref, tol=1e-2)
 
 
 def test_attention_rejects_unsupported_shapes():
-    qkv = torch.zeros(8, 3 * 72, device=DEV).bfloat16()
+    qkv = torch.zeros(8, 3 * 96, device=DEV).bfloat16()
     with pytest.raises(ops.MMError):
-        ops.attention_fwd(qkv, 1, 8, 1, 72, 0.1)
+        ops.attention_fwd(qkv, 1, 8, 1, 96, 0.1)
 
 
 def test_weighted_expert_sum():
