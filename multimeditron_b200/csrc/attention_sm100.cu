@@ -107,6 +107,26 @@ __device__ __forceinline__ void tc_mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, 
       : "memory");
 }
 
+// Optional phase trace (tools/attn_trace.py; compiled in only with -DMM_ATTN_TRACE): block 0 records clock64()
+// stamps of one softmax warp per stream and of the MMA issuer.
+#ifdef MM_ATTN_TRACE
+__device__ long long* g_attn_trace = nullptr;  // 3 roles x 1024 (id, clock) pairs; fire-and-forget stores
+__device__ __forceinline__ void attn_trace(int role, uint32_t& k, int id) {
+  if (g_attn_trace && k < 1024) {
+    g_attn_trace[(role * 1024 + k) * 2] = id;
+    g_attn_trace[(role * 1024 + k) * 2 + 1] = clock64();
+    ++k;
+  }
+}
+#define TRACE_DECL uint32_t trc_k = 0;
+#define TRACE_SM(id) do { if (blockIdx.x == 0 && q == 0 && lane == 0) attn_trace(s, trc_k, (id) + 16 * s); } while (0)
+#define TRACE_MMA(id) do { if (blockIdx.x == 0) attn_trace(2, trc_k, id); } while (0)
+#else
+#define TRACE_DECL
+#define TRACE_SM(id)
+#define TRACE_MMA(id)
+#endif
+
 template <int HD, int BKV>
 __global__ void __launch_bounds__(kAttnThreads, 1)
     attention_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnParams p) {
@@ -217,6 +237,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       constexpr uint32_t idesc_pvx = umma_idesc_bf16(kBQ, 16, 0, 1);  // the 16 extra head columns
       uint32_t qi[2] = {0, 0}, it_s[2] = {0, 0}, it_pv[2] = {0, 0};
       RingPos cur{0, 0};
+      TRACE_DECL
       auto issue_s = [&](int s, int stage) {
         mbar_wait(&bars->s_empty[s], (it_s[s] & 1) ^ 1);
         tc_fence_after();
@@ -234,6 +255,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
           tc_mma_f16_ss(d, umma_desc_sw32(qx, 16, 256), umma_desc_sw32(kx, 16, 256), idesc_s, 1);
         }
         tc_commit(&bars->s_full[s]);
+        TRACE_MMA(6 + s);
         ++it_s[s];
       };
       auto issue_pv = [&](int s, int kt, int stage) {
@@ -252,6 +274,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
             tc_mma_f16_ts(d + 64, a + k * 8, umma_desc_sw32(vx_addr + k * 512, 256, 256), idesc_pvx, (kt | k) != 0);
         }
         tc_commit(&bars->pv_done[s]);
+        TRACE_MMA(8 + s);
         ++it_pv[s];
       };
       for (int u = blockIdx.x; u < units; u += gridDim.x) {
@@ -301,6 +324,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     const uint32_t t_O = tmem_base + Cfg::kColO + s * HD + lane_sel;
     const float sl2 = p.scale_log2;
     uint32_t it = 0;
+    TRACE_DECL
     for (int u = blockIdx.x; u < units; u += gridDim.x) {
       const int b = u / p.heads, h = u - b * p.heads;
       for (int qt = s; qt < nq; qt += 2) {
@@ -309,6 +333,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         for (int kt = 0; kt < nkv; ++kt, ++it) {
           const int valid = p.T - kt * BKV;  // columns >= valid are padding (only in the last kv tile)
           mbar_wait(&bars->s_full[s], it & 1);
+          TRACE_SM(0);
           tc_fence_after();
           uint32_t sv[BKV];
           if (warp_live) {
@@ -316,6 +341,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
             for (int c = 0; c < NCH; ++c)
               if (c * 32 < valid) tmem_ld_32x32b_x32(t_S + c * 32, sv + c * 32);
             tc_wait_ld();
+            TRACE_SM(1);
           }
           // the S accumulator now lives in registers: hand it back for the next QK^T right away
           tc_fence_before();
@@ -361,10 +387,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
               }
             }
             sum = (sum0 + sum1) + (sum2 + sum3);
+            TRACE_SM(2);
           }
           // P (TMEM) and the O accumulator are free once PV of the previous iteration retired
           if (it > 0) {
             mbar_wait(&bars->pv_done[s], (it - 1) & 1);
+            TRACE_SM(3);
             tc_fence_after();
           }
           if (warp_live) {
@@ -390,10 +418,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
             for (int c = 0; c < BKV / 64; ++c) tmem_st_32x32b_x32(t_P + c * 32, pk + c * 32);
             if (BKV % 64) tmem_st_32x32b_x16(t_P + (BKV / 64) * 32, pk + (BKV / 64) * 32);
             tc_wait_st();
+            TRACE_SM(4);
           }
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&bars->p_full[s]);
+          TRACE_SM(5);
         }
         // ---- epilogue of the q tile: O / l -> bf16 -> global ----
         mbar_wait(&bars->pv_done[s], (it - 1) & 1);
@@ -481,6 +511,13 @@ static int launch_attention(const void* qkv, const AttnParams& p, cudaStream_t s
 }  // namespace mm
 
 using namespace mm;
+
+#ifdef MM_ATTN_TRACE
+extern "C" int mm_attention_trace_set(long long* buf) {
+  if (cudaMemcpyToSymbol(g_attn_trace, &buf, sizeof(buf)) != cudaSuccess) return MM_ERR_CUDA;
+  return MM_OK;
+}
+#endif
 
 extern "C" int64_t mm_attention_head_stride(int64_t head_dim) {
   if (head_dim == 64) return 64;

@@ -24,8 +24,10 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--shape", default="cfg2")
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--T", type=int, default=0)
     a = ap.parse_args()
     B, T, nh, hd = SHAPES[a.shape]
+    T = a.T or T
     dev = torch.device("cuda:0")
     hs = ops.attn_head_stride(hd) if hasattr(ops, "attn_head_stride") else hd
     g = torch.Generator().manual_seed(0)
