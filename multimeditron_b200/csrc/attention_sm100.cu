@@ -127,6 +127,47 @@ __device__ __forceinline__ void attn_trace(int role, uint32_t& k, int id) {
 #define TRACE_MMA(id)
 #endif
 
+// non-blocking phase test (event loops of the producer and the MMA issuer poll several barriers)
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void named_bar_sync(int id, int count) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+__device__ __forceinline__ void named_bar_arrive(int id, int count) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+
+// Work decomposition shared by every role.  The CTA owns units u_i = blockIdx.x + i*gridDim.x.  A K/V "group" is
+// what travels through the ring together: the whole unit when it fits (resident), else one query pair of it.
+// Stream s owns, in group g, the query tiles first_qt(s,g) + 2j, j < ntiles(s,g).  Both streams always work inside
+// the same group (the exp-phase token below keeps them half a step apart), so ring slots are never awaited across
+// groups by a stream that runs ahead.
+struct AttnSched {
+  int nkv, nq, npair, n_units, ngroups;
+  bool resident;
+  __device__ __forceinline__ int unit_ord(int g) const { return resident ? g : g / npair; }
+  __device__ __forceinline__ int first_qt(int s, int g) const {
+    return resident ? s : 2 * (g - unit_ord(g) * npair) + s;
+  }
+  __device__ __forceinline__ int slots(int /*g*/) const { return resident ? npair : 1; }  // tile slots per stream
+  __device__ __forceinline__ int ntiles(int s, int g) const {
+    const int f = first_qt(s, g);
+    if (f >= nq) return 0;
+    return resident ? (nq - f + 1) >> 1 : 1;
+  }
+};
+
 template <int HD, int BKV>
 __global__ void __launch_bounds__(kAttnThreads, 1)
     attention_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnParams p) {
@@ -141,11 +182,15 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   AttnBars* bars = reinterpret_cast<AttnBars*>(sKV + NS * Cfg::kStageBytes);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nkv = (p.T + BKV - 1) / BKV;
-  const int nq = (p.T + kBQ - 1) / kBQ;
-  const int npair = (nq + 1) >> 1;
   const int units = p.B * p.heads;
-  const bool resident = nkv <= NS;  // whole unit fits in the ring: load K/V once per unit
+  AttnSched sc;
+  sc.nkv = (p.T + BKV - 1) / BKV;
+  sc.nq = (p.T + kBQ - 1) / kBQ;
+  sc.npair = (sc.nq + 1) >> 1;
+  sc.resident = sc.nkv <= NS;  // whole unit fits in the ring: load K/V once per unit
+  sc.n_units = ((int)blockIdx.x < units) ? (units - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  sc.ngroups = sc.n_units * (sc.resident ? 1 : sc.npair);
+  const int nkv = sc.nkv;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&maps.q_main);
@@ -158,7 +203,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < NS; ++i) {
       mbar_init(&bars->kv_full[i], 1);
-      mbar_init(&bars->kv_empty[i], 1);
+      mbar_init(&bars->kv_empty[i], 2);  // one release per stream (real tile: tcgen05.commit; none: plain arrive)
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&bars->q_full[s], 1);
@@ -185,135 +230,155 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   // (the role code is nested inside the two branches so that ptxas allocates each region with its own budget)
   if (warp < 4) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
-  if (warp == 0) {
-    // =========================== TMA producer ===========================
-    if (elect_one_sync()) {
-      RingPos rp{0, 0};
-      uint32_t qi[2] = {0, 0};
-      auto load_q = [&](int s, int qt, int h, int b) {
-        mbar_wait(&bars->q_empty[s], (qi[s] & 1) ^ 1);
-        mbar_arrive_expect_tx(&bars->q_full[s], Cfg::kQMain + Cfg::kQX);
-        tma_load_3d(sQ + s * Cfg::kQMain, &maps.q_main, &bars->q_full[s], h * HD, qt * kBQ, b);
-        if (HDX) tma_load_3d(sQX + s * Cfg::kQX, &maps.q_x, &bars->q_full[s], h * HD + 64, qt * kBQ, b);
-        ++qi[s];
-      };
-      auto load_kv = [&](int kt, int h, int b) {
-        mbar_wait(&bars->kv_empty[rp.stage], rp.phase ^ 1);
-        uint64_t* full = &bars->kv_full[rp.stage];
-        uint8_t* st = sKV + rp.stage * Cfg::kStageBytes;
-        mbar_arrive_expect_tx(full, Cfg::kStageBytes);
-        tma_load_3d(st, &maps.kv_main, full, p.Dp + h * HD, kt * BKV, b);
-        tma_load_3d(st + Cfg::kKMain, &maps.kv_main, full, 2 * p.Dp + h * HD, kt * BKV, b);
-        if (HDX) {
-          tma_load_3d(st + 2 * Cfg::kKMain, &maps.kv_x, full, p.Dp + h * HD + 64, kt * BKV, b);
-          tma_load_3d(st + 2 * Cfg::kKMain + Cfg::kKX, &maps.kv_x, full, 2 * p.Dp + h * HD + 64, kt * BKV, b);
-        }
-        rp.advance<NS>();
-      };
-      for (int u = blockIdx.x; u < units; u += gridDim.x) {
-        const int b = u / p.heads, h = u - b * p.heads;
-        for (int pi = 0; pi < npair; ++pi) {
-          const bool two = 2 * pi + 1 < nq;
-          if (pi == 0 || !resident) {
-            for (int kt = 0; kt < nkv; ++kt) {
-              load_kv(kt, h, b);
-              if (kt == 0) {  // Q right behind the first K/V tile so S(0) can start early
-                load_q(0, 2 * pi, h, b);
-                if (two) load_q(1, 2 * pi + 1, h, b);
+    if (warp == 0) {
+      // =========================== TMA producer (event loop: K/V ring, Q of stream 0, Q of stream 1) =============
+      if (elect_one_sync()) {
+        int kv_g = 0, kv_kt = 0, kv_stage = 0;
+        uint32_t kv_phase = 0;
+        int q_g[2] = {0, 0}, q_j[2] = {0, 0};
+        uint32_t q_n[2] = {0, 0};
+        for (int s = 0; s < 2; ++s)
+          while (q_g[s] < sc.ngroups && sc.ntiles(s, q_g[s]) == 0) ++q_g[s];
+        while (kv_g < sc.ngroups || q_g[0] < sc.ngroups || q_g[1] < sc.ngroups) {
+          if (kv_g < sc.ngroups && mbar_test(&bars->kv_empty[kv_stage], kv_phase ^ 1)) {
+            const int u = blockIdx.x + sc.unit_ord(kv_g) * gridDim.x;
+            const int b = u / p.heads, h = u - b * p.heads;
+            uint64_t* full = &bars->kv_full[kv_stage];
+            uint8_t* st = sKV + kv_stage * Cfg::kStageBytes;
+            mbar_arrive_expect_tx(full, Cfg::kStageBytes);
+            tma_load_3d(st, &maps.kv_main, full, p.Dp + h * HD, kv_kt * BKV, b);
+            tma_load_3d(st + Cfg::kKMain, &maps.kv_main, full, 2 * p.Dp + h * HD, kv_kt * BKV, b);
+            if (HDX) {
+              tma_load_3d(st + 2 * Cfg::kKMain, &maps.kv_x, full, p.Dp + h * HD + 64, kv_kt * BKV, b);
+              tma_load_3d(st + 2 * Cfg::kKMain + Cfg::kKX, &maps.kv_x, full, 2 * p.Dp + h * HD + 64, kv_kt * BKV, b);
+            }
+            if (++kv_stage == NS) kv_stage = 0, kv_phase ^= 1u;
+            if (++kv_kt == nkv) kv_kt = 0, ++kv_g;
+          }
+#pragma unroll
+          for (int s = 0; s < 2; ++s) {
+            if (q_g[s] < sc.ngroups && mbar_test(&bars->q_empty[s], (q_n[s] & 1) ^ 1)) {
+              const int g = q_g[s];
+              const int u = blockIdx.x + sc.unit_ord(g) * gridDim.x;
+              const int b = u / p.heads, h = u - b * p.heads;
+              const int qt = sc.first_qt(s, g) + 2 * q_j[s];
+              mbar_arrive_expect_tx(&bars->q_full[s], Cfg::kQMain + Cfg::kQX);
+              tma_load_3d(sQ + s * Cfg::kQMain, &maps.q_main, &bars->q_full[s], h * HD, qt * kBQ, b);
+              if (HDX) tma_load_3d(sQX + s * Cfg::kQX, &maps.q_x, &bars->q_full[s], h * HD + 64, qt * kBQ, b);
+              ++q_n[s];
+              if (++q_j[s] == sc.ntiles(s, g)) {
+                q_j[s] = 0;
+                ++q_g[s];
+                while (q_g[s] < sc.ngroups && sc.ntiles(s, q_g[s]) == 0) ++q_g[s];
               }
             }
-          } else {
-            load_q(0, 2 * pi, h, b);
-            if (two) load_q(1, 2 * pi + 1, h, b);
+          }
+        }
+      }
+    } else if (warp == 1) {
+      // =========================== MMA issuer (event loop over the two streams) ===========================
+      if (elect_one_sync()) {
+        constexpr uint32_t idesc_s = umma_idesc_bf16(kBQ, BKV, 0, 0);
+        constexpr uint32_t idesc_pv = umma_idesc_bf16(kBQ, 64, 0, 1);   // B (= V) is MN-major
+        constexpr uint32_t idesc_pvx = umma_idesc_bf16(kBQ, 16, 0, 1);  // the 16 extra head columns
+        TRACE_DECL
+        // per-stream cursor: group, tile within group, next S / next PV kv step, and barrier use counts
+        int cg[2] = {0, 0}, cj[2] = {0, 0}, cnt[2], ks[2] = {0, 0}, kp[2] = {0, 0};
+        uint32_t n_tile[2] = {0, 0}, n_s[2] = {0, 0}, n_pv[2] = {0, 0};
+        cnt[0] = sc.ngroups ? sc.ntiles(0, 0) : 0;
+        cnt[1] = sc.ngroups ? sc.ntiles(1, 0) : 0;
+        auto slot_of = [&](int g, int kt, int& stage, uint32_t& phase) {
+          const int seq = g * nkv + kt;
+          const int r = seq / NS;
+          stage = seq - r * NS;
+          phase = (uint32_t)r & 1u;
+        };
+        while (cg[0] < sc.ngroups || cg[1] < sc.ngroups) {
+#pragma unroll
+          for (int s = 0; s < 2; ++s) {
+            if (cg[s] >= sc.ngroups) continue;
+            int stage;
+            uint32_t phase;
+            if (cnt[s] == 0) {
+              // this stream has no query tile in the group: only hand its share of the K/V slots back
+              slot_of(cg[s], kp[s], stage, phase);
+              if (mbar_test(&bars->kv_full[stage], phase)) {
+                mbar_arrive(&bars->kv_empty[stage]);
+                if (++kp[s] == nkv) {
+                  kp[s] = 0;
+                  if (++cg[s] < sc.ngroups) cnt[s] = sc.ntiles(s, cg[s]);
+                }
+              }
+              continue;
+            }
+            // ---- S(ks) = Q K^T : needs Q (first step), the K/V slot, and the S accumulator back from the softmax
+            if (ks[s] < nkv) {
+              slot_of(cg[s], ks[s], stage, phase);
+              if ((ks[s] != 0 || mbar_test(&bars->q_full[s], n_tile[s] & 1)) &&
+                  mbar_test(&bars->kv_full[stage], phase) && mbar_test(&bars->s_empty[s], (n_s[s] & 1) ^ 1)) {
+                tc_fence_after();
+                const uint32_t q_addr = smem_u32(sQ + s * Cfg::kQMain);
+                const uint32_t k_addr = smem_u32(sKV + stage * Cfg::kStageBytes);
+                const uint32_t d = tmem_base + Cfg::kColS + s * BKV;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  tc_mma_f16_ss(d, umma_desc_sw128(q_addr + k * 32, 16, 1024),
+                                umma_desc_sw128(k_addr + k * 32, 16, 1024), idesc_s, k != 0);
+                }
+                if (HDX) {
+                  const uint32_t qx = smem_u32(sQX + s * Cfg::kQX);
+                  const uint32_t kx = smem_u32(sKV + stage * Cfg::kStageBytes + 2 * Cfg::kKMain);
+                  tc_mma_f16_ss(d, umma_desc_sw32(qx, 16, 256), umma_desc_sw32(kx, 16, 256), idesc_s, 1);
+                }
+                tc_commit(&bars->s_full[s]);
+                TRACE_MMA(6 + s);
+                ++n_s[s];
+                if (++ks[s] == nkv) tc_commit(&bars->q_empty[s]);  // Q tile free once these MMAs retire
+              }
+            }
+            // ---- O += P(kp) V : needs P from the softmax (and, for the first step, the drained O accumulator)
+            if (kp[s] < ks[s]) {
+              if (mbar_test(&bars->p_full[s], n_pv[s] & 1) &&
+                  (kp[s] != 0 || mbar_test(&bars->o_empty[s], (n_tile[s] & 1) ^ 1))) {
+                tc_fence_after();
+                slot_of(cg[s], kp[s], stage, phase);
+                const uint32_t v_addr = smem_u32(sKV + stage * Cfg::kStageBytes + Cfg::kKMain);
+                const uint32_t vx_addr = smem_u32(sKV + stage * Cfg::kStageBytes + 2 * Cfg::kKMain + Cfg::kKX);
+                const uint32_t d = tmem_base + Cfg::kColO + s * HD;
+                const uint32_t a = tmem_base + Cfg::kColP + s * (BKV / 2);
+                const uint32_t acc0 = kp[s] != 0;
+#pragma unroll
+                for (int k = 0; k < BKV / 16; ++k) {
+                  // A = P from TMEM (16 bf16 = 8 columns per k-step); B = V MN-major, 16 kv rows per k-step
+                  tc_mma_f16_ts(d, a + k * 8, umma_desc_sw128(v_addr + k * 2048, 1024, 1024), idesc_pv, acc0 | (k != 0));
+                  if (HDX)
+                    tc_mma_f16_ts(d + 64, a + k * 8, umma_desc_sw32(vx_addr + k * 512, 256, 256), idesc_pvx,
+                                  acc0 | (k != 0));
+                }
+                tc_commit(&bars->pv_done[s]);
+                TRACE_MMA(8 + s);
+                ++n_pv[s];
+                if (cj[s] == cnt[s] - 1) tc_commit(&bars->kv_empty[stage]);  // last tile of this stream on the slot
+                if (++kp[s] == nkv) {  // tile finished: next tile / next group
+                  ks[s] = kp[s] = 0;
+                  ++n_tile[s];
+                  if (++cj[s] == cnt[s]) {
+                    cj[s] = 0;
+                    if (++cg[s] < sc.ngroups) cnt[s] = sc.ntiles(s, cg[s]);
+                  }
+                }
+              }
+            }
           }
         }
       }
     }
-  } else if (warp == 1) {
-    // =========================== MMA issuer ===========================
-    if (elect_one_sync()) {
-      constexpr uint32_t idesc_s = umma_idesc_bf16(kBQ, BKV, 0, 0);
-      constexpr uint32_t idesc_pv = umma_idesc_bf16(kBQ, 64, 0, 1);   // B (= V) is MN-major
-      constexpr uint32_t idesc_pvx = umma_idesc_bf16(kBQ, 16, 0, 1);  // the 16 extra head columns
-      uint32_t qi[2] = {0, 0}, it_s[2] = {0, 0}, it_pv[2] = {0, 0};
-      RingPos cur{0, 0};
-      TRACE_DECL
-      auto issue_s = [&](int s, int stage) {
-        mbar_wait(&bars->s_empty[s], (it_s[s] & 1) ^ 1);
-        tc_fence_after();
-        const uint32_t q_addr = smem_u32(sQ + s * Cfg::kQMain);
-        const uint32_t k_addr = smem_u32(sKV + stage * Cfg::kStageBytes);
-        const uint32_t d = tmem_base + Cfg::kColS + s * BKV;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          tc_mma_f16_ss(d, umma_desc_sw128(q_addr + k * 32, 16, 1024), umma_desc_sw128(k_addr + k * 32, 16, 1024),
-                        idesc_s, k != 0);
-        }
-        if (HDX) {
-          const uint32_t qx = smem_u32(sQX + s * Cfg::kQX);
-          const uint32_t kx = smem_u32(sKV + stage * Cfg::kStageBytes + 2 * Cfg::kKMain);
-          tc_mma_f16_ss(d, umma_desc_sw32(qx, 16, 256), umma_desc_sw32(kx, 16, 256), idesc_s, 1);
-        }
-        tc_commit(&bars->s_full[s]);
-        TRACE_MMA(6 + s);
-        ++it_s[s];
-      };
-      auto issue_pv = [&](int s, int kt, int stage) {
-        mbar_wait(&bars->p_full[s], it_pv[s] & 1);
-        if (kt == 0) mbar_wait(&bars->o_empty[s], (qi[s] & 1) ^ 1);  // previous tile's epilogue drained O
-        tc_fence_after();
-        const uint32_t v_addr = smem_u32(sKV + stage * Cfg::kStageBytes + Cfg::kKMain);
-        const uint32_t vx_addr = smem_u32(sKV + stage * Cfg::kStageBytes + 2 * Cfg::kKMain + Cfg::kKX);
-        const uint32_t d = tmem_base + Cfg::kColO + s * HD;
-        const uint32_t a = tmem_base + Cfg::kColP + s * (BKV / 2);
-#pragma unroll
-        for (int k = 0; k < BKV / 16; ++k) {
-          // A = P from TMEM (16 bf16 = 8 columns per k-step); B = V MN-major, 16 kv rows per k-step
-          tc_mma_f16_ts(d, a + k * 8, umma_desc_sw128(v_addr + k * 2048, 1024, 1024), idesc_pv, (kt | k) != 0);
-          if (HDX)
-            tc_mma_f16_ts(d + 64, a + k * 8, umma_desc_sw32(vx_addr + k * 512, 256, 256), idesc_pvx, (kt | k) != 0);
-        }
-        tc_commit(&bars->pv_done[s]);
-        TRACE_MMA(8 + s);
-        ++it_pv[s];
-      };
-      for (int u = blockIdx.x; u < units; u += gridDim.x) {
-        const RingPos ubase = cur;
-        for (int pi = 0; pi < npair; ++pi) {
-          const int ns = (2 * pi + 1 < nq) ? 2 : 1;  // active streams in this pair
-          const bool fresh = (pi == 0) || !resident;       // K/V tiles arrive during this pair
-          const bool release = (pi == npair - 1) || !resident;
-          RingPos st = resident ? ubase : cur;
-          int prev_stage = 0;
-          for (int s = 0; s < ns; ++s) mbar_wait(&bars->q_full[s], qi[s] & 1);
-          tc_fence_after();
-          for (int kt = 0; kt < nkv; ++kt) {
-            if (fresh) mbar_wait(&bars->kv_full[st.stage], st.phase);
-            tc_fence_after();
-            for (int s = 0; s < ns; ++s) {
-              issue_s(s, st.stage);
-              if (kt == nkv - 1) tc_commit(&bars->q_empty[s]);
-            }
-            if (kt >= 1) {
-              for (int s = 0; s < ns; ++s) issue_pv(s, kt - 1, prev_stage);
-              if (release) tc_commit(&bars->kv_empty[prev_stage]);
-            }
-            prev_stage = st.stage;
-            st.advance<NS>();
-          }
-          for (int s = 0; s < ns; ++s) {
-            issue_pv(s, nkv - 1, prev_stage);
-            ++qi[s];
-          }
-          if (release) tc_commit(&bars->kv_empty[prev_stage]);
-          cur = st;
-        }
-      }
-    }
-  }
   } else {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
     // =========================== softmax / correction / epilogue (stream = warpgroup) ===========================
+    // The two streams take turns in the MUFU-bound exp phase (named barriers 1 and 2 pass a token back and forth),
+    // which keeps them half a step out of phase: while one stream runs its exps the other does its TMEM loads,
+    // row max, P store and barrier traffic.  A stream without a tile in a slot just passes the token on.
     constexpr int NCH = BKV / 32;
     const int s = (warp - 4) >> 2;
     const int q = warp & 3;
@@ -325,9 +390,20 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     const float sl2 = p.scale_log2;
     uint32_t it = 0;
     TRACE_DECL
-    for (int u = blockIdx.x; u < units; u += gridDim.x) {
+    if (s == 1) named_bar_arrive(1, 256);  // stream 0 goes first
+    for (int g = 0; g < sc.ngroups; ++g) {
+      const int u = blockIdx.x + sc.unit_ord(g) * gridDim.x;
       const int b = u / p.heads, h = u - b * p.heads;
-      for (int qt = s; qt < nq; qt += 2) {
+      const int nt = sc.ntiles(s, g);
+      for (int j = 0; j < sc.slots(g); ++j) {
+        if (j >= nt) {  // no tile in this slot: keep the token moving
+          for (int kt = 0; kt < nkv; ++kt) {
+            named_bar_sync(1 + s, 256);
+            named_bar_arrive(2 - s, 256);
+          }
+          continue;
+        }
+        const int qt = sc.first_qt(s, g) + 2 * j;
         const bool warp_live = qt * kBQ + q * 32 < p.T;  // warps whose 32 rows are all padding only keep the protocol
         float m_run = -INFINITY, l_run = 0.f;            // running max (raw score units) and row sum
         for (int kt = 0; kt < nkv; ++kt, ++it) {
@@ -349,52 +425,57 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
           if (lane == 0) mbar_arrive(&bars->s_empty[s]);
           uint32_t pk[BKV / 2];
           float m_new = m_run, sum = 0.f;
+          float m_scaled = 0.f;
           if (warp_live) {
             if (valid < BKV) {
 #pragma unroll
-              for (int j = 0; j < BKV; ++j)
-                if (j >= valid) sv[j] = 0xff800000u;  // -inf
+              for (int jj = 0; jj < BKV; ++jj)
+                if (jj >= valid) sv[jj] = 0xff800000u;  // -inf
             }
             float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-            for (int j = 0; j < BKV; j += 8) {
-              mx0 = fmaxf(mx0, fmaxf(__uint_as_float(sv[j + 0]), __uint_as_float(sv[j + 1])));
-              mx1 = fmaxf(mx1, fmaxf(__uint_as_float(sv[j + 2]), __uint_as_float(sv[j + 3])));
-              mx2 = fmaxf(mx2, fmaxf(__uint_as_float(sv[j + 4]), __uint_as_float(sv[j + 5])));
-              mx3 = fmaxf(mx3, fmaxf(__uint_as_float(sv[j + 6]), __uint_as_float(sv[j + 7])));
+            for (int jj = 0; jj < BKV; jj += 8) {
+              mx0 = fmaxf(mx0, fmaxf(__uint_as_float(sv[jj + 0]), __uint_as_float(sv[jj + 1])));
+              mx1 = fmaxf(mx1, fmaxf(__uint_as_float(sv[jj + 2]), __uint_as_float(sv[jj + 3])));
+              mx2 = fmaxf(mx2, fmaxf(__uint_as_float(sv[jj + 4]), __uint_as_float(sv[jj + 5])));
+              mx3 = fmaxf(mx3, fmaxf(__uint_as_float(sv[jj + 6]), __uint_as_float(sv[jj + 7])));
             }
             const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
             // the reference max only moves when it grows by more than the threshold (keeps O rescales rare)
             if ((mx - m_run) * sl2 > kRescaleThreshold) m_new = mx;  // also true for m_run = -inf
-            const float m_scaled = m_new * sl2;
+            m_scaled = m_new * sl2;
+          }
+          named_bar_sync(1 + s, 256);  // ---- exp phase: this stream's turn on the MUFU ----
+          if (warp_live) {
             float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
 #pragma unroll
             for (int c = 0; c < NCH; ++c) {
               if (c * 32 < valid) {
 #pragma unroll
-                for (int j = c * 32; j < c * 32 + 32; j += 4) {
-                  const float p0 = ex2(fmaf(__uint_as_float(sv[j + 0]), sl2, -m_scaled));
-                  const float p1 = ex2(fmaf(__uint_as_float(sv[j + 1]), sl2, -m_scaled));
-                  const float p2 = ex2(fmaf(__uint_as_float(sv[j + 2]), sl2, -m_scaled));
-                  const float p3 = ex2(fmaf(__uint_as_float(sv[j + 3]), sl2, -m_scaled));
+                for (int jj = c * 32; jj < c * 32 + 32; jj += 4) {
+                  const float p0 = ex2(fmaf(__uint_as_float(sv[jj + 0]), sl2, -m_scaled));
+                  const float p1 = ex2(fmaf(__uint_as_float(sv[jj + 1]), sl2, -m_scaled));
+                  const float p2 = ex2(fmaf(__uint_as_float(sv[jj + 2]), sl2, -m_scaled));
+                  const float p3 = ex2(fmaf(__uint_as_float(sv[jj + 3]), sl2, -m_scaled));
                   sum0 += p0, sum1 += p1, sum2 += p2, sum3 += p3;
-                  pk[j >> 1] = pack_bf16x2(p0, p1);
-                  pk[(j >> 1) + 1] = pack_bf16x2(p2, p3);
+                  pk[jj >> 1] = pack_bf16x2(p0, p1);
+                  pk[(jj >> 1) + 1] = pack_bf16x2(p2, p3);
                 }
               } else {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) pk[c * 16 + j] = 0u;
+                for (int jj = 0; jj < 16; ++jj) pk[c * 16 + jj] = 0u;
               }
             }
             sum = (sum0 + sum1) + (sum2 + sum3);
-            TRACE_SM(2);
           }
+          named_bar_arrive(2 - s, 256);  // ---- token to the other stream ----
+          TRACE_SM(2);
           // P (TMEM) and the O accumulator are free once PV of the previous iteration retired
           if (it > 0) {
             mbar_wait(&bars->pv_done[s], (it - 1) & 1);
-            TRACE_SM(3);
             tc_fence_after();
           }
+          TRACE_SM(3);
           if (warp_live) {
             if (kt > 0) {
               const float alpha = ex2((m_run - m_new) * sl2);  // 1 when the max did not move
@@ -406,7 +487,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
                   tmem_ld_32x32b_x16(t_O + c * 16, o);
                   tc_wait_ld();
 #pragma unroll
-                  for (int j = 0; j < 16; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * alpha);
+                  for (int jj = 0; jj < 16; ++jj) o[jj] = __float_as_uint(__uint_as_float(o[jj]) * alpha);
                   tmem_st_32x32b_x16(t_O + c * 16, o);
                 }
               }
@@ -439,14 +520,14 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
             tc_wait_ld();
             if (t < p.T) {
 #pragma unroll
-              for (int j = 0; j < 2; ++j) {
-                if (c * 16 + j * 8 < p.hd_out) {
+              for (int jj = 0; jj < 2; ++jj) {
+                if (c * 16 + jj * 8 < p.hd_out) {
                   int4 v;
-                  v.x = (int)pack_bf16x2(__uint_as_float(o[j * 8 + 0]) * inv_l, __uint_as_float(o[j * 8 + 1]) * inv_l);
-                  v.y = (int)pack_bf16x2(__uint_as_float(o[j * 8 + 2]) * inv_l, __uint_as_float(o[j * 8 + 3]) * inv_l);
-                  v.z = (int)pack_bf16x2(__uint_as_float(o[j * 8 + 4]) * inv_l, __uint_as_float(o[j * 8 + 5]) * inv_l);
-                  v.w = (int)pack_bf16x2(__uint_as_float(o[j * 8 + 6]) * inv_l, __uint_as_float(o[j * 8 + 7]) * inv_l);
-                  *reinterpret_cast<int4*>(dst + c * 16 + j * 8) = v;
+                  v.x = (int)pack_bf16x2(__uint_as_float(o[jj * 8 + 0]) * inv_l, __uint_as_float(o[jj * 8 + 1]) * inv_l);
+                  v.y = (int)pack_bf16x2(__uint_as_float(o[jj * 8 + 2]) * inv_l, __uint_as_float(o[jj * 8 + 3]) * inv_l);
+                  v.z = (int)pack_bf16x2(__uint_as_float(o[jj * 8 + 4]) * inv_l, __uint_as_float(o[jj * 8 + 5]) * inv_l);
+                  v.w = (int)pack_bf16x2(__uint_as_float(o[jj * 8 + 6]) * inv_l, __uint_as_float(o[jj * 8 + 7]) * inv_l);
+                  *reinterpret_cast<int4*>(dst + c * 16 + jj * 8) = v;
                 }
               }
             }
@@ -457,6 +538,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         if (lane == 0) mbar_arrive(&bars->o_empty[s]);
       }
     }
+    if (s == 0) named_bar_sync(1, 256);  // absorb stream 1's last token pass
   }
 
   tc_fence_before();
