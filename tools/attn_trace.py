@@ -28,11 +28,16 @@ ev = [(i, c) for i, c in ev if c != 0]
 t0 = min(c for _, c in ev)
 ev.sort(key=lambda e: e[1])
 names = {0: "s_full", 1: "S_regs", 2: "exps", 3: "pv_done", 4: "P_st", 5: "p_full"}
+ev = [e for e in ev if 6 <= e[0] <= 13] if len(sys.argv) > 3 else ev
 for i, c in ev[:int(sys.argv[2]) if len(sys.argv) > 2 else 160]:
     if i in (6, 7):
         tag = f"MMA  S{i - 6} issued"
     elif i in (8, 9):
         tag = f"MMA  PV{i - 8} issued"
+    elif i in (10, 11):
+        tag = f"MMA  S{i - 10} begin"
+    elif i in (12, 13):
+        tag = f"MMA  PV{i - 12} begin"
     else:
         tag = f"SM{i // 16}   {names[i % 16]}"
     print(f"{c - t0:8d}  {tag}")
