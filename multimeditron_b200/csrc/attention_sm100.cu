@@ -29,6 +29,10 @@ constexpr int kBQ = 128;
 constexpr int kAttnThreads = 384;          // w0 TMA, w1 MMA, w2 TMEM alloc, w3 idle, w4-7 stream 0, w8-11 stream 1
 constexpr float kRescaleThreshold = 8.0f;  // log2 units: P <= 2^8, harmless in bf16/fp32
 constexpr int kMaxStages = 8;
+#ifndef MM_ATTN_POLL_NS
+#define MM_ATTN_POLL_NS 32
+#endif
+constexpr unsigned kPollSleepNs = MM_ATTN_POLL_NS;  // idle back-off of the two polling service threads
 
 template <int HD, int BKV>
 struct AttnCfg {
@@ -240,7 +244,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         for (int s = 0; s < 2; ++s)
           while (q_g[s] < sc.ngroups && sc.ntiles(s, q_g[s]) == 0) ++q_g[s];
         while (kv_g < sc.ngroups || q_g[0] < sc.ngroups || q_g[1] < sc.ngroups) {
+          bool progress = false;
           if (kv_g < sc.ngroups && mbar_test(&bars->kv_empty[kv_stage], kv_phase ^ 1)) {
+            progress = true;
             const int u = blockIdx.x + sc.unit_ord(kv_g) * gridDim.x;
             const int b = u / p.heads, h = u - b * p.heads;
             uint64_t* full = &bars->kv_full[kv_stage];
@@ -258,6 +264,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
 #pragma unroll
           for (int s = 0; s < 2; ++s) {
             if (q_g[s] < sc.ngroups && mbar_test(&bars->q_empty[s], (q_n[s] & 1) ^ 1)) {
+              progress = true;
               const int g = q_g[s];
               const int u = blockIdx.x + sc.unit_ord(g) * gridDim.x;
               const int b = u / p.heads, h = u - b * p.heads;
@@ -273,6 +280,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
               }
             }
           }
+          if (!progress) __nanosleep(kPollSleepNs);  // leave the issue slots of this scheduler to the softmax warp
         }
       }
     } else if (warp == 1) {
@@ -294,6 +302,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
           phase = (uint32_t)r & 1u;
         };
         while (cg[0] < sc.ngroups || cg[1] < sc.ngroups) {
+          bool progress = false;
 #pragma unroll
           for (int s = 0; s < 2; ++s) {
             if (cg[s] >= sc.ngroups) continue;
@@ -304,6 +313,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
               slot_of(cg[s], kp[s], stage, phase);
               if (mbar_test(&bars->kv_full[stage], phase)) {
                 mbar_arrive(&bars->kv_empty[stage]);
+                progress = true;
                 if (++kp[s] == nkv) {
                   kp[s] = 0;
                   if (++cg[s] < sc.ngroups) cnt[s] = sc.ntiles(s, cg[s]);
@@ -317,6 +327,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
               if ((ks[s] != 0 || mbar_test(&bars->q_full[s], n_tile[s] & 1)) &&
                   mbar_test(&bars->kv_full[stage], phase) && mbar_test(&bars->s_empty[s], (n_s[s] & 1) ^ 1)) {
                 tc_fence_after();
+                progress = true;
                 const uint32_t q_addr = smem_u32(sQ + s * Cfg::kQMain);
                 const uint32_t k_addr = smem_u32(sKV + stage * Cfg::kStageBytes);
                 const uint32_t d = tmem_base + Cfg::kColS + s * BKV;
@@ -341,6 +352,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
               if (mbar_test(&bars->p_full[s], n_pv[s] & 1) &&
                   (kp[s] != 0 || mbar_test(&bars->o_empty[s], (n_tile[s] & 1) ^ 1))) {
                 tc_fence_after();
+                progress = true;
                 slot_of(cg[s], kp[s], stage, phase);
                 const uint32_t v_addr = smem_u32(sKV + stage * Cfg::kStageBytes + Cfg::kKMain);
                 const uint32_t vx_addr = smem_u32(sKV + stage * Cfg::kStageBytes + 2 * Cfg::kKMain + Cfg::kKX);
@@ -370,6 +382,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
               }
             }
           }
+          if (!progress) __nanosleep(kPollSleepNs);
         }
       }
     }
@@ -390,7 +403,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     const float sl2 = p.scale_log2;
     uint32_t it = 0;
     TRACE_DECL
-    if (s == 1) named_bar_arrive(1, 256);  // stream 0 goes first
+    // one token per scheduler (warp q of stream 0 and warp q of stream 1 share scheduler q): barriers 1 + 2q + s
+    const int tok_mine = 1 + 2 * q + s, tok_other = 1 + 2 * q + (s ^ 1);
+    if (s == 1) named_bar_arrive(tok_other, 64);  // stream 0 goes first
     for (int g = 0; g < sc.ngroups; ++g) {
       const int u = blockIdx.x + sc.unit_ord(g) * gridDim.x;
       const int b = u / p.heads, h = u - b * p.heads;
@@ -398,8 +413,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       for (int j = 0; j < sc.slots(g); ++j) {
         if (j >= nt) {  // no tile in this slot: keep the token moving
           for (int kt = 0; kt < nkv; ++kt) {
-            named_bar_sync(1 + s, 256);
-            named_bar_arrive(2 - s, 256);
+            named_bar_sync(tok_mine, 64);
+            named_bar_arrive(tok_other, 64);
           }
           continue;
         }
@@ -445,31 +460,49 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
             if ((mx - m_run) * sl2 > kRescaleThreshold) m_new = mx;  // also true for m_run = -inf
             m_scaled = m_new * sl2;
           }
-          named_bar_sync(1 + s, 256);  // ---- exp phase: this stream's turn on the MUFU ----
+          TRACE_SM(14);
+          named_bar_sync(tok_mine, 64);  // ---- exp phase: this warp's turn on its scheduler's MUFU ----
+          TRACE_SM(15);
           if (warp_live) {
             float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
+            if (valid >= BKV) {
+              // full tile: one straight-line block, so that ptxas interleaves the ex2 of the whole row (a block per
+              // 32-column chunk drains the MUFU pipe at every boundary: measured 1900 vs 1250 clk per tile)
 #pragma unroll
-            for (int c = 0; c < NCH; ++c) {
-              if (c * 32 < valid) {
+              for (int jj = 0; jj < BKV; jj += 4) {
+                const float p0 = ex2(fmaf(__uint_as_float(sv[jj + 0]), sl2, -m_scaled));
+                const float p1 = ex2(fmaf(__uint_as_float(sv[jj + 1]), sl2, -m_scaled));
+                const float p2 = ex2(fmaf(__uint_as_float(sv[jj + 2]), sl2, -m_scaled));
+                const float p3 = ex2(fmaf(__uint_as_float(sv[jj + 3]), sl2, -m_scaled));
+                sum0 += p0, sum1 += p1, sum2 += p2, sum3 += p3;
+                pk[jj >> 1] = pack_bf16x2(p0, p1);
+                pk[(jj >> 1) + 1] = pack_bf16x2(p2, p3);
+              }
+            } else {
+              // last (partial) kv tile: chunks that are all padding are skipped
 #pragma unroll
-                for (int jj = c * 32; jj < c * 32 + 32; jj += 4) {
-                  const float p0 = ex2(fmaf(__uint_as_float(sv[jj + 0]), sl2, -m_scaled));
-                  const float p1 = ex2(fmaf(__uint_as_float(sv[jj + 1]), sl2, -m_scaled));
-                  const float p2 = ex2(fmaf(__uint_as_float(sv[jj + 2]), sl2, -m_scaled));
-                  const float p3 = ex2(fmaf(__uint_as_float(sv[jj + 3]), sl2, -m_scaled));
-                  sum0 += p0, sum1 += p1, sum2 += p2, sum3 += p3;
-                  pk[jj >> 1] = pack_bf16x2(p0, p1);
-                  pk[(jj >> 1) + 1] = pack_bf16x2(p2, p3);
+              for (int c = 0; c < NCH; ++c) {
+                if (c * 32 < valid) {
+#pragma unroll
+                  for (int jj = c * 32; jj < c * 32 + 32; jj += 4) {
+                    const float p0 = ex2(fmaf(__uint_as_float(sv[jj + 0]), sl2, -m_scaled));
+                    const float p1 = ex2(fmaf(__uint_as_float(sv[jj + 1]), sl2, -m_scaled));
+                    const float p2 = ex2(fmaf(__uint_as_float(sv[jj + 2]), sl2, -m_scaled));
+                    const float p3 = ex2(fmaf(__uint_as_float(sv[jj + 3]), sl2, -m_scaled));
+                    sum0 += p0, sum1 += p1, sum2 += p2, sum3 += p3;
+                    pk[jj >> 1] = pack_bf16x2(p0, p1);
+                    pk[(jj >> 1) + 1] = pack_bf16x2(p2, p3);
+                  }
+                } else {
+#pragma unroll
+                  for (int jj = 0; jj < 16; ++jj) pk[c * 16 + jj] = 0u;
                 }
-              } else {
-#pragma unroll
-                for (int jj = 0; jj < 16; ++jj) pk[c * 16 + jj] = 0u;
               }
             }
             sum = (sum0 + sum1) + (sum2 + sum3);
           }
-          named_bar_arrive(2 - s, 256);  // ---- token to the other stream ----
           TRACE_SM(2);
+          named_bar_arrive(tok_other, 64);  // ---- token to the other stream's warp on this scheduler ----
           // P (TMEM) and the O accumulator are free once PV of the previous iteration retired
           if (it > 0) {
             mbar_wait(&bars->pv_done[s], (it - 1) & 1);
@@ -538,7 +571,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         if (lane == 0) mbar_arrive(&bars->o_empty[s]);
       }
     }
-    if (s == 0) named_bar_sync(1, 256);  // absorb stream 1's last token pass
+    if (s == 0) named_bar_sync(tok_mine, 64);  // absorb stream 1's last token pass
   }
 
   tc_fence_before();

@@ -27,7 +27,7 @@ ev = buf.view(-1, 2).cpu().tolist()
 ev = [(i, c) for i, c in ev if c != 0]
 t0 = min(c for _, c in ev)
 ev.sort(key=lambda e: e[1])
-names = {0: "s_full", 1: "S_regs", 2: "exps", 3: "pv_done", 4: "P_st", 5: "p_full"}
+names = {0: "s_full", 1: "S_regs", 2: "exps", 3: "pv_done", 4: "P_st", 5: "p_full", 14: "max_done", 15: "token"}
 ev = [e for e in ev if 6 <= e[0] <= 13] if len(sys.argv) > 3 else ev
 for i, c in ev[:int(sys.argv[2]) if len(sys.argv) > 2 else 160]:
     if i in (6, 7):
