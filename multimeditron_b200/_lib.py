@@ -11,7 +11,8 @@ import re
 from pathlib import Path
 
 _HERE = Path(__file__).resolve().parent
-LIB_PATH = _HERE / "csrc" / "libmm_b200.so"
+# MM_B200_LIB: developer override used by tools/ to A/B two builds of the library in one GPU session
+LIB_PATH = Path(os.environ["MM_B200_LIB"]) if os.environ.get("MM_B200_LIB") else _HERE / "csrc" / "libmm_b200.so"
 HEADER_PATH = _HERE.parent / "include" / "mm_b200.h"
 
 _lib = None
