@@ -27,10 +27,25 @@ if ROOT not in sys.path:
 
 METRIC, UNIT = "image_embed_tokens_per_s", "tokens/s"
 WORKLOADS = {
-    # name: (tower, llm hidden, images/GPU, text tokens per row, vocab)
+    # name: (tower, llm hidden, images/GPU, text tokens per row, vocab[, images per row, fixed seq_len])
     "cfg2_clip_l14_336_llama8b": ("clip_l14_336", 4096, 256, 64, 128_258),
     "cfg1_clip_b32_tiny_llama": ("clip_b32", 512, 8, 4, 206),
+    # BASELINE configs[2]: SigLIP so400m/14-384 -> Qwen2.5-7B hidden 3584 (64 images/GPU x 8 = 512)
+    "cfg3_siglip_so400m_qwen7b": ("siglip_so400m_384", 3584, 64, 64, 152_064),
+    # BASELINE configs[3]: interleaved rows, 4 images per 8192-token row (cfg2 encoder), 64 rows = 256 images
+    "cfg4_interleaved_8k": ("clip_l14_336", 4096, 256, 0, 128_258, 4, 8192),
 }
+
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` capture of this command at
+# cfg2 B=256 (profiles/r01c_ncu_full_summary.txt): GEMM = mean over one encoder layer's four launches
+# (fc2 1.807, qkv 1.161, out-proj 0.867, fc1 1.467 GB); splice mover = the embed-gather launch of the step.
+NCU_TRAFFIC = {"cfg2_clip_l14_336_llama8b": {"gemm": 1.3256e9, "attention": 1.1849e9, "layernorm": 0.5464e9}}
+
+
+def workload(wl):
+    w = WORKLOADS[wl]
+    return dict(tower=w[0], H=w[1], images=w[2], n_text=w[3], V=w[4], per_row=w[5] if len(w) > 5 else 1,
+                seq_len=w[6] if len(w) > 6 else None)
 
 
 def peaks():
@@ -103,11 +118,14 @@ class ClockSampler:
 
 # ------------------------------------------------------------------------------------------------------------------
 def build_inputs(wl, seed, images, torch, synth, TOWERS):
-    tower, H, _, n_text, V = WORKLOADS[wl]
+    w = workload(wl)
+    tower, H, n_text, V, per_row = w["tower"], w["H"], w["n_text"], w["V"], w["per_row"]
     cfg = TOWERS[tower]
-    S = cfg.num_patches + 2 + n_text
+    S = w["seq_len"] or cfg.num_patches + 2 + n_text
+    assert images % per_row == 0, "images per GPU must be a multiple of the images per row"
     att, start, end, pad = V - 2, V - 4, V - 3, V - 1   # the added special tokens sit at the end of the vocabulary
-    ids, _ = synth.make_sequences(images, S, 1, cfg.num_patches, V - 4, att, start, end, pad, seed=seed)
+    ids, _ = synth.make_sequences(images // per_row, S, per_row, cfg.num_patches, V - 4, att, start, end, pad, seed=seed,
+                                  min_len=(6144 if w["seq_len"] else None))
     px = synth.make_pixels(cfg, images, seed=seed)
     return cfg, H, V, S, att, ids, px
 
@@ -124,7 +142,9 @@ def cpu_reference_leg(wl, sample_images, steps, warmup, threads, dtype_name="flo
     dt = getattr(torch, dtype_name)
     sd = {k: v.to(dt) for k, v in synth.make_modality_state_dict(cfg, H, seed=0).items()}
     table = (torch.randn(V, H, generator=torch.Generator().manual_seed(1)) * 0.02).to(dt)
-    ranges = [splice_oracle.compute_token_range(ids[b].numpy(), [cfg.num_patches], att) for b in range(sample_images)]
+    per_row = workload(wl)["per_row"]
+    ranges = [splice_oracle.compute_token_range(ids[b].numpy(), [cfg.num_patches] * per_row, att)
+              for b in range(ids.shape[0])]
     bidx, trng = map(torch.from_numpy, splice_oracle.collator_indices(ranges))
     inputs = [px[i] for i in range(sample_images)]
 
@@ -152,7 +172,8 @@ def run_reference(args):
     threads = os.cpu_count() or 1
     sample = args.cpu_sample
     toks, ms, desc = cpu_reference_leg(args.workload, sample, max(1, args.steps), max(0, min(args.warmup, 1)), threads)
-    tower, H, ipg, n_text, V = WORKLOADS[args.workload]
+    w = workload(args.workload)
+    tower, H, ipg, n_text, V = w["tower"], w["H"], w["images"], w["n_text"], w["V"]
     line = {"impl": "reference", "metric": METRIC, "value": toks, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic (seeded N(0,1) pixels, random-init weights)",
@@ -182,7 +203,8 @@ def run_b200(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    tower, H, images, n_text, V = WORKLOADS[args.workload]
+    w = workload(args.workload)
+    tower, H, images, n_text, V = w["tower"], w["H"], w["images"], w["n_text"], w["V"]
     if args.images_per_gpu:
         images = args.images_per_gpu
     cfg, H, V, S, att, ids, px = build_inputs(args.workload, 100 + rank, images, torch, synth, TOWERS)
@@ -275,9 +297,9 @@ def run_b200(args):
         "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16", "data": "synthetic (seeded N(0,1) pixels, random-init weights; no network for checkpoints)",
         "config": {"workload": args.workload, "tower": tower, "llm_hidden": H, "images_per_gpu": images,
-                   "global_images": total_images, "seq_len": S, "tokens_per_image": P, "parallelism": f"sample-shard x{world}",
+                   "global_images": total_images, "rows_per_gpu": ids.shape[0], "seq_len": S, "tokens_per_image": P, "parallelism": f"sample-shard x{world}",
                    "l2": "inputs larger than L2 (pixels %.0f MB, inputs_embeds %.0f MB per step)" % (
-                       px.numel() * 4 / 1e6, images * S * H * 2 / 1e6),
+                       px.numel() * 4 / 1e6, ids.shape[0] * S * H * 2 / 1e6),
                    "positions": "device prefix sum", "splice": "fused into the last projector GEMM epilogue"},
         "clocks": clocks,
         "e2e": {"value": total_images * P / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
@@ -286,7 +308,10 @@ def run_b200(args):
         "gpu_launches_per_step": launches_per_step,
         "roofline": {"kernel": "gemm_bf16_tn_kernel<false> (tcgen05 GEMM, %d launches/step)" % (n_gemm // max(1, args.steps)),
                      "bound": "tensor", "achieved": gemm_tf, "peak": pk["tf_sust"], "unit": "TFLOP/s",
-                     "frac": gemm_tf / pk["tf_sust"], "traffic": None,
+                     "frac": gemm_tf / pk["tf_sust"],
+                     "traffic": NCU_TRAFFIC.get(args.workload, {}).get("gemm") if images == w["images"] else None,
+                     "traffic_src": "ncu --set full, mean bytes per launch over one encoder layer's 4 GEMMs "
+                                    "(profiles/r01c_ncu_full_summary.txt)",
                      "peak_kind": f"{pk['src']} sustained cuBLAS bf16 (kernel timed inside a long step)",
                      "frac_of_burst": gemm_tf / pk["tf_burst"]},
         "path_tensor": {"achieved": path_tf, "unit": "TFLOP/s", "frac_of_sustained": path_tf / pk["tf_sust"],

@@ -63,6 +63,8 @@ class TowerConfig:
 TOWERS = {
     # test-sized tower (head_dim 64 like the real ones)
     "tiny": TowerConfig("clip", 32, 8, 128, 256, 2, 2),
+    # test-sized SigLIP tower: head_dim 72, MLP width not a multiple of 64, conv bias, no CLS, post-LN, tanh-GELU
+    "tiny_siglip": TowerConfig("siglip", 56, 14, 144, 304, 2, 2, 1e-6, "gelu_pytorch_tanh"),
     "clip_b32": TowerConfig("clip", 224, 32, 768, 3072, 12, 12),
     "clip_l14_336": TowerConfig("clip", 336, 14, 1024, 4096, 24, 16),
     "siglip_so400m_384": TowerConfig("siglip", 384, 14, 1152, 4304, 27, 16, 1e-6, "gelu_pytorch_tanh"),

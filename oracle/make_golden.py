@@ -103,6 +103,39 @@ def gen_modality(ref):
                             pseed=pseed, **out)
 
 
+@torch.no_grad()
+def gen_siglip():
+    """Row A9 (no reference class): HF SiglipVisionModel.last_hidden_state (all tokens, post-LN applied,
+    HF:models/siglip/modeling_siglip.py:604-625) + the reference MLPProjector (projectors/mlp.py:33-59)."""
+    from transformers import SiglipVisionConfig, SiglipVisionModel
+    from multimeditron.model.projectors.mlp import MLPProjector
+    name, hidden, batch, wseed, pseed = "tiny_siglip", 96, 3, 5, 9
+    cfg = TOWERS[name]
+    sd32 = synth.make_modality_state_dict(cfg, hidden, seed=wseed)
+    pixels = synth.make_pixels(cfg, batch, seed=pseed)
+    hf = SiglipVisionModel(SiglipVisionConfig(
+        hidden_size=cfg.hidden_size, intermediate_size=cfg.intermediate_size, num_hidden_layers=cfg.num_hidden_layers,
+        num_attention_heads=cfg.num_attention_heads, image_size=cfg.image_size, patch_size=cfg.patch_size,
+        layer_norm_eps=cfg.layer_norm_eps, hidden_act=cfg.hidden_act)).eval()
+    pre = "feature_extractor."
+    missing, unexpected = hf.load_state_dict({k[len(pre):]: v for k, v in sd32.items() if k.startswith(pre)}, strict=False)
+    assert not unexpected and all(k.startswith("vision_model.head.") for k in missing), (missing, unexpected)
+    proj = MLPProjector(cfg.hidden_size, hidden, dtype=torch.float32)
+    proj.load_state_dict({k[len("projector."):]: v for k, v in sd32.items() if k.startswith("projector.")})
+    out = {}
+    for dt, tag in ((torch.float32, "fp32"), (torch.bfloat16, "bf16")):
+        hf, proj = hf.to(dt), proj.to(dt)
+        y = proj(hf(pixels.to(dt)).last_hidden_state)
+        sd = {k: v.to(dt) for k, v in sd32.items()}
+        o = vit_oracle.image_modality_forward(sd, cfg, [pixels[i] for i in range(batch)])
+        assert torch.equal(y, o), f"siglip oracle != HF ({tag})"
+        out[tag] = y
+    err = (out["bf16"].float() - out["fp32"]).abs().max().item()
+    print(f"[modality {name}] out {tuple(out['fp32'].shape)} absmax {out['fp32'].abs().max():.4f} bf16-vs-fp32 maxabs {err:.3e}")
+    np.savez_compressed(os.path.join(GOLD, f"modality_{name}.npz"), hidden=hidden, batch=batch, wseed=wseed, pseed=pseed,
+                        out_fp32=out["fp32"].numpy(), out_bf16_bits=bf16_bits(out["bf16"]))
+
+
 SPLICE_CASES = [
     # name, batch, seq, images/row, tokens/image, hidden, padding, min_len, table dtype, proj dtype
     ("right_1img", 3, 40, 1, 9, 32, "right", 24, "float32", "float32"),
@@ -264,9 +297,15 @@ def main():
     torch.manual_seed(0)
     torch.set_num_threads(max(1, os.cpu_count() or 1))
     ref = ref_shim.import_reference()
-    gen_splice(ref)
-    gen_modality(ref)
-    gen_moe(ref)
+    only = sys.argv[1:]
+    if not only or "splice" in only:
+        gen_splice(ref)
+    if not only or "modality" in only:
+        gen_modality(ref)
+    if not only or "siglip" in only:
+        gen_siglip()
+    if not only or "moe" in only:
+        gen_moe(ref)
     print("golden written to", GOLD)
 
 

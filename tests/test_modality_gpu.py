@@ -28,7 +28,7 @@ def _modality(name, hidden, wseed):
     return m, sd
 
 
-@pytest.mark.parametrize("name", ["tiny", "clip_b32"])
+@pytest.mark.parametrize("name", ["tiny", "clip_b32", "tiny_siglip"])
 def test_modality_forward_vs_reference_golden(golden_dir, name):
     g = np.load(os.path.join(golden_dir, f"modality_{name}.npz"))
     hidden, batch = int(g["hidden"]), int(g["batch"])

@@ -15,7 +15,7 @@ def _bits(t):
     return t.contiguous().view(torch.int16).numpy()
 
 
-@pytest.mark.parametrize("name", ["tiny", "clip_b32"])
+@pytest.mark.parametrize("name", ["tiny", "clip_b32", "tiny_siglip"])
 def test_modality_oracle_matches_reference_golden(golden_dir, name):
     g = np.load(os.path.join(golden_dir, f"modality_{name}.npz"))
     cfg = TOWERS[name]
