@@ -180,6 +180,32 @@ int mm_attention_fwd(const void* qkv, void* out, int64_t B, int64_t T, int64_t h
 int mm_weighted_expert_sum(const void* x, const float* w, const int32_t* perm, void* out,
                            int64_t E, int64_t B, int64_t P, int64_t D, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Image pre-processing on the device — bit-exact byte/integer work, HBM-bound
+ * ------------------------------------------------------------------------------------------ */
+
+/*
+ * mm_preprocess_images — raw uint8 HWC images (ragged batch) -> the pixel tensor the image embedder consumes.
+ * Replaces the CPU work of `ImageProcessor.process` (src/multimeditron/model/modalities/image_modality.py:96):
+ * transformers 5.5.0 CLIPImageProcessor / SiglipImageProcessor on the torchvision backend
+ * (HF:image_processing_backends.py:372-420): uint8 antialiased bicubic resize (ATen's separable int16-weight
+ * kernel: horizontal pass, uint8 intermediate, vertical pass), center crop, (x - mean*255) / (std*255) in fp32;
+ * with out_dtype MM_BF16 the fp32 value is rounded RNE exactly as HF:models/clip/modeling_clip.py:208-209 casts it.
+ *   src    device bytes, 4-byte aligned; image i is [H,W,3] uint8 at src + desc[i][0]
+ *   desc   device int64 [B][8] = {src_off, H, W, out_h, out_w, crop_top, crop_left, tmp_off}: the image is resized
+ *          to (out_h,out_w) and the S x S window at (crop_top,crop_left) is produced (out_h,out_w >= S);
+ *          tmp_off = byte offset of this image's [H,S,3] intermediate inside `tmp`
+ *   kmax   >= 2*ceil(2*max(1, in/out)) + 1 over every image and axis (taps per output pixel)
+ *   max_h, max_w   largest H / W in the batch (grid and shared-memory sizing)
+ *   ws     mm_preprocess_workspace_bytes(B,S,kmax) device bytes; tmp  sum_i H_i*S*3 device bytes
+ *   mean255, std255   HOST float[3]: image_mean*(1/rescale_factor), image_std*(1/rescale_factor) in fp32
+ *   out    [B,3,S,S] fp32 (MM_F32, the reference's `pixel_values`) or bf16 (MM_BF16)
+ */
+int64_t mm_preprocess_workspace_bytes(int64_t B, int64_t S, int64_t kmax);
+int mm_preprocess_images(const void* src, const int64_t* desc, int64_t B, int64_t S, int64_t kmax,
+                         int64_t max_h, int64_t max_w, void* ws, void* tmp, const float* mean255,
+                         const float* std255, void* out, int out_dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

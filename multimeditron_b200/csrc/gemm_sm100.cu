@@ -535,7 +535,7 @@ extern "C" int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64
 extern "C" int mm_patch_embed(const void* pixels, int pixel_dtype, int64_t B, int64_t img, int64_t patch,
                               const void* weight, int64_t ldw, const void* conv_bias, const void* pos_emb,
                               const void* cls, void* out, int64_t D, void* stream) {
-  if (B < 0 || img <= 0 || patch <= 0 || img % patch || D <= 0 || D % 8) return MM_ERR_BAD_ARG;
+  if (B < 0 || img <= 0 || patch <= 0 || img < patch || D <= 0 || D % 8) return MM_ERR_BAD_ARG;  // img % patch != 0 is fine: the conv (stride = kernel) drops the remainder, SigLIP 384/14 -> 27x27
   if (B == 0) return MM_OK;
   if (!pixels || !weight || !pos_emb || !out) return MM_ERR_BAD_ARG;
   if (pixel_dtype != MM_F32 && pixel_dtype != MM_BF16) return MM_ERR_BAD_ARG;

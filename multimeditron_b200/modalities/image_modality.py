@@ -13,6 +13,7 @@ from typing import Any, Dict, List, Optional
 import torch
 
 from ..configs import TOWERS, TowerConfig
+from ..preprocess import DevicePreprocessor
 from ..vit import ProjectorWeights, TowerRunner, TowerWeights
 from .base import AutoModality, BaseModality, BaseModalityConfig, BaseModalityProcessor
 from .constants import MODALITY_VALUE_KEY, NUM_EMBEDDINGS_KEY, POSITION_IDS_KEY
@@ -35,11 +36,15 @@ def resolve_tower(clip_name) -> TowerConfig:
 
 class B200ImageConfig(BaseModalityConfig):
     def __init__(self, hidden_size: int = 4096, clip_name="openai/clip-vit-large-patch14",
-                 projection_type: str = "mlp", use_2d_position_ids: bool = False, **kwargs):
+                 projection_type: str = "mlp", use_2d_position_ids: bool = False,
+                 device_preprocess: bool = False, **kwargs):
         super().__init__(modality_type="image", hidden_size=hidden_size, **kwargs)
         self.clip_name = clip_name
         self.projection_type = projection_type
         self.use_2d_position_ids = use_2d_position_ids
+        # True: `process` hands over the raw uint8 [H,W,3] image and resize/crop/normalise run on the GPU
+        # (mm_preprocess_images, bit-exact with the HF torchvision-backend processor) — SURVEY §8(f) rank 1
+        self.device_preprocess = device_preprocess
 
 
 class B200ImageProcessor(BaseModalityProcessor):
@@ -62,6 +67,9 @@ class B200ImageProcessor(BaseModalityProcessor):
         image = modality[MODALITY_VALUE_KEY]
         if torch.is_tensor(image):
             out[MODALITY_VALUE_KEY] = image
+        elif getattr(self.config, "device_preprocess", False):
+            import numpy as np
+            out[MODALITY_VALUE_KEY] = torch.from_numpy(np.array(image.convert("RGB"), dtype=np.uint8))  # convert_to_rgb
         else:
             if self.image_processor is None:
                 raise ValueError("PIL input needs a checkpoint directory with an image processor (clip_name)")
@@ -90,6 +98,7 @@ class B200ImageModality(BaseModality):
         self._runner: Optional[TowerRunner] = None
         self._staging: Optional[torch.Tensor] = None
         self._staging_event = None
+        self._pre: Optional[DevicePreprocessor] = None
         self._frozen = True
         if state_dict is not None:
             self.load_reference_state_dict(state_dict, device or torch.device("cuda", torch.cuda.current_device()))
@@ -123,6 +132,10 @@ class B200ImageModality(BaseModality):
         if torch.is_tensor(inputs):
             return inputs.to(dev, non_blocking=True)
         inputs = list(inputs)
+        if len(inputs) and inputs[0].dtype == torch.uint8:   # raw [H,W,3] images: pre-process on the device
+            if self._pre is None:
+                self._pre = DevicePreprocessor.for_tower(self.tower)
+            return self._pre(inputs, dev, torch.bfloat16)
         if len(inputs) and inputs[0].is_cuda:
             return torch.stack(inputs, dim=0)
         # one cached pinned staging buffer + one async H2D instead of the reference's pageable, synchronous

@@ -292,3 +292,26 @@ def weighted_expert_sum(x: torch.Tensor, w: torch.Tensor, perm: torch.Tensor | N
         rc = lib.mm_weighted_expert_sum(_ptr(x), _ptr(w), _ptr(perm), _ptr(out), E, B, P, D, _stream())
     _check(rc, "mm_weighted_expert_sum")
     return out
+
+
+# --------------------------------------------------------------------------------- image pre-processing
+def preprocess_images(src: torch.Tensor, desc: torch.Tensor, size: int, kmax: int, max_h: int, max_w: int,
+                      tmp_bytes: int, mean255, std255, out_dtype=torch.float32) -> torch.Tensor:
+    """src uint8 device bytes (packed HWC images), desc int64 [B,8] device (include/mm_b200.h) -> [B,3,size,size]."""
+    import ctypes as C
+    _cuda(src, desc)
+    lib = _lib.load()
+    B = desc.shape[0]
+    assert src.dtype == torch.uint8 and desc.dtype == torch.int64 and desc.is_contiguous() and desc.shape[1] == 8
+    out = torch.empty(B, 3, size, size, dtype=out_dtype, device=src.device)
+    ws = torch.empty(max(256, lib.mm_preprocess_workspace_bytes(B, size, kmax)), dtype=torch.uint8, device=src.device)
+    tmp = torch.empty(max(256, tmp_bytes), dtype=torch.uint8, device=src.device)
+    m = (C.c_float * 3)(*[float(v) for v in mean255])
+    s = (C.c_float * 3)(*[float(v) for v in std255])
+    global LAUNCHES
+    LAUNCHES += 2  # three kernels per call (the context manager counts one)
+    with _timed("mm_preprocess_images", float(src.numel()) + out.numel() * out.element_size()):
+        rc = lib.mm_preprocess_images(_ptr(src), _ptr(desc), B, size, kmax, max_h, max_w, _ptr(ws), _ptr(tmp), m, s,
+                                      _ptr(out), _dt(out), _stream())
+    _check(rc, "mm_preprocess_images")
+    return out

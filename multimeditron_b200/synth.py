@@ -123,3 +123,13 @@ def make_sequences(batch: int, seq_len: int, images_per_row: int, tokens_per_ima
             ids[b, seq_len - length:] = row
             mask[b, seq_len - length:] = True
     return ids, mask
+
+
+def make_raw_image(i: int, h: int, w: int):
+    """Seeded raw uint8 [h,w,3] image (noise; every third one a smooth ramp) for the pre-processing tests/goldens."""
+    import numpy as np
+    img = np.random.default_rng(100 + i).integers(0, 256, (h, w, 3), dtype=np.uint8)
+    if i % 3 == 0:
+        yy, xx = np.mgrid[0:h, 0:w]
+        img = np.stack([(yy * 255 // max(1, h - 1)), (xx * 255 // max(1, w - 1)), ((yy + xx) % 256)], -1).astype(np.uint8)
+    return img

@@ -136,6 +136,42 @@ def gen_siglip():
                         out_fp32=out["fp32"].numpy(), out_bf16_bits=bf16_bits(out["bf16"]))
 
 
+PREPROCESS_CASES = [  # (H, W, size, square) raw uint8 images, seeded
+    (37, 53, 56, False), (300, 400, 224, False), (640, 480, 224, False), (224, 224, 224, False), (1000, 333, 224, False),
+    (90, 120, 224, False), (225, 224, 224, False), (500, 700, 384, True), (100, 80, 384, True), (336, 336, 336, False),
+]
+
+
+def gen_preprocess():
+    """`ImageProcessor.process` (image_modality.py:96) = HF CLIPImageProcessor / SiglipImageProcessor (transformers
+    5.5.0, torchvision backend) on seeded uint8 PIL images; oracle/preprocess_oracle.py must match it bit for bit."""
+    from PIL import Image
+    from transformers import CLIPImageProcessor, SiglipImageProcessor
+    from oracle import preprocess_oracle as po
+    out = {"cases": np.array(PREPROCESS_CASES, np.int64)}
+    for i, (h, w, size, square) in enumerate(PREPROCESS_CASES):
+        img = synth.make_raw_image(i, h, w)   # noise, every third one a smooth ramp
+        if square:
+            p = SiglipImageProcessor(size={"height": size, "width": size})
+            mean = std = (0.5, 0.5, 0.5)
+        else:
+            p = CLIPImageProcessor(size={"shortest_edge": size}, crop_size={"height": size, "width": size})
+            mean, std = po.OPENAI_CLIP_MEAN, po.OPENAI_CLIP_STD
+        ref = p(images=Image.fromarray(img), return_tensors="pt")["pixel_values"][0].numpy()
+        got = po.clip_preprocess(img, size, mean, std, square=bool(square))
+        assert np.array_equal(ref.view(np.int32), got.view(np.int32)), f"preprocess oracle != HF for case {i}"
+        # store the uint8 stage (compact) — the fp32 value is an exact function of it
+        m, s = po.fused_mean_std(mean, std)
+        u8 = np.rint(ref * s[:, None, None] + m[:, None, None]).astype(np.uint8)
+        assert np.array_equal(((u8.astype(np.float32) - m[:, None, None]) / s[:, None, None]).view(np.int32), ref.view(np.int32))
+        import hashlib
+        out[f"sha_{i}"] = np.frombuffer(hashlib.sha256(ref.tobytes()).digest(), np.uint8)   # digest of the fp32 tensor
+        if size <= 56:
+            out[f"u8_{i}"] = u8
+    np.savez_compressed(os.path.join(GOLD, "preprocess.npz"), **out)
+    print(f"[preprocess] {len(PREPROCESS_CASES)} cases pinned against the HF processors")
+
+
 SPLICE_CASES = [
     # name, batch, seq, images/row, tokens/image, hidden, padding, min_len, table dtype, proj dtype
     ("right_1img", 3, 40, 1, 9, 32, "right", 24, "float32", "float32"),
@@ -304,6 +340,8 @@ def main():
         gen_modality(ref)
     if not only or "siglip" in only:
         gen_siglip()
+    if not only or "preprocess" in only:
+        gen_preprocess()
     if not only or "moe" in only:
         gen_moe(ref)
     print("golden written to", GOLD)

@@ -109,6 +109,8 @@ def test_gemm_rejects_bad_arguments():
     (3, 224, 32, 768, True, False, torch.float32),     # CLIP-B/32
     (2, 336, 14, 1024, True, False, torch.float32),    # CLIP-L/14-336 (K=588, padded to 640)
     (2, 56, 14, 256, False, True, torch.bfloat16),     # SigLIP-style: conv bias, no CLS, bf16 pixels
+    (2, 384, 14, 1152, False, True, torch.float32),    # SigLIP so400m: 384 % 14 != 0, the conv drops the last 6 pixels
+    (3, 61, 14, 128, True, False, torch.bfloat16),     # odd image size, remainder 5
 ])
 def test_patch_embed(B, img, p, D, cls, bias, dt):
     G = img // p
