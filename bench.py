@@ -182,7 +182,7 @@ def run_reference(args):
             "cpu_baseline": {"value": toks, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc},
             "e2e": {"value": toks, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -328,7 +328,7 @@ def run_b200(args):
         toks, _, desc = cpu_reference_leg(args.workload, args.cpu_sample, 1, 1, threads)
         line["cpu_baseline"] = {"value": toks, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -344,10 +344,27 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=4, help="images per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: anything a library prints there (e.g. NCCL's version banner) goes to stderr
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
         run_b200(args)
+
+
+_JSON_FD = None
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
 
 
 if __name__ == "__main__":

@@ -143,6 +143,31 @@ int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, con
                      const int32_t* out_row_map, int64_t n_out_rows, void* stream);
 
 /*
+ * mm_gemm_ln_bias_act — the same GEMM with LayerNorm folded in on either side, so that the encoder layer's two
+ * LayerNorm passes (HF:models/clip/modeling_clip.py:370,379; siglip :341,350) cost no HBM traffic of their own:
+ *     LN(x)·Wᵀ + b  =  rstd · (x·W''ᵀ) + b',    W'' = gamma ⊙ W with every row re-centred to sum to zero
+ *                                               (so the −mean·Σ_k W'' term vanishes inside the MMA),
+ *                                               b'_n = b_n + Σ_k beta_k·W[n,k]
+ *   producer side  stats_out != NULL: after bias/act/residual, every stored row also emits, per 64-column chunk,
+ *                  (Σ v, Σ v²) of the bf16 values it stored: stats_out [rows of C][mm_gemm_row_stats_slots(N)] float2
+ *                  (slot count rounded up to 16 = whole 128-byte lines; the buffer must be ZERO-initialised once,
+ *                  unused slots are never written).
+ *   consumer side  ln_stats != NULL: A is the RAW residual stream x, W is W'' and `bias` is b' (both packed once at
+ *                  load time, bf16; W'' is rounded with error feedback along k so that its bf16 row sums stay ~0),
+ *                  the epilogue rebuilds rstd of row m from ln_stats [M][mm_gemm_row_stats_slots(K)] (summed in a
+ *                  fixed order: bit-reproducible) and forms bf16(rstd·acc + b').  Rounding then follows
+ *                  mm_gemm_bias_act.
+ * Numerics: the reference rounds LN(x) to bf16 before the GEMM; here gamma ⊙ W is rounded to bf16 instead and
+ * LN itself stays in fp32 — same error scale (2^-9 relative per operand), covered by the stated bf16 tolerance.
+ */
+int64_t mm_gemm_row_stats_slots(int64_t N);
+int mm_gemm_ln_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias,
+                        void* C, int64_t ldc, int64_t M, int64_t N, int64_t K, int act,
+                        const void* residual, int64_t ldr, const int32_t* out_row_map,
+                        int64_t n_out_rows, void* stats_out, const void* ln_stats, float ln_eps,
+                        void* stream);
+
+/*
  * mm_patch_embed — im2col-free implicit GEMM of the patch convolution
  *   (Conv2d k=s=patch; HF:models/clip/modeling_clip.py:148-154,208-210, siglip :124-130,163-164)
  * fused with flatten/transpose, +position embedding and the CLS row (modeling_clip.py:210-218).

@@ -32,6 +32,8 @@ SIGNATURES = {
     "mm_embed_gather": (i32, [vp, i64, i64, i32, vp, i64, vp, vp, vp]),
     "mm_layernorm": (i32, [vp, vp, vp, vp, i64, i64, f32, i64, i64, i64, vp]),
     "mm_gemm_bias_act": (i32, [vp, i64, vp, i64, vp, vp, i64, i64, i64, i64, i32, vp, i64, i64, i64, vp, i64, vp]),
+    "mm_gemm_row_stats_slots": (i64, [i64]),
+    "mm_gemm_ln_bias_act": (i32, [vp, i64, vp, i64, vp, vp, i64, i64, i64, i64, i32, vp, i64, vp, i64, vp, vp, f32, vp]),
     "mm_patch_embed": (i32, [vp, i32, i64, i64, i64, vp, i64, vp, vp, vp, vp, i64, vp]),
     "mm_attention_head_stride": (i64, [i64]),
     "mm_attention_fwd": (i32, [vp, vp, i64, i64, i64, i64, f32, vp]),
@@ -59,7 +61,11 @@ def load() -> C.CDLL:
         )
     lib = C.CDLL(os.fspath(LIB_PATH))
     for name, (res, args) in SIGNATURES.items():
-        fn = getattr(lib, name)
+        fn = getattr(lib, name, None)
+        if fn is None:
+            if os.environ.get("MM_B200_LIB"):   # A/B against an older build: bind what it has
+                continue
+            raise RuntimeError(f"{LIB_PATH} does not export {name}: rebuild it (python __graft_entry__.py)")
         fn.restype = res
         fn.argtypes = args
     _lib = lib

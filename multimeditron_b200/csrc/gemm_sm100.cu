@@ -64,6 +64,13 @@ struct GemmParams {
   int map_in, map_out, map_off;  // formula row map: out_row = (m / map_in) * map_out + map_off + m % map_in
   int act;
   int tiles_m, tiles_n;
+  // LayerNorm folded into the GEMM (mm_gemm_ln_bias_act):  LN(x)·Wᵀ + b = rstd·(x·W''ᵀ) + b'
+  // with W'' = gamma ⊙ W re-centred so that every row sums to zero (the mean term cancels inside the MMA).
+  //   producer side: per 64-column chunk (sum, sum of squares) of the rows this GEMM writes
+  //   consumer side: row statistics of A from those partials -> rstd; `bias` is b'
+  float2* stats_out;        // [rows of C][slots] or NULL
+  const float2* ln_stats;   // [M][slots] or NULL
+  float ln_eps, ln_inv_k;
   // gather-A (patch embed) only
   const void* pixels;
   int pixel_is_f32;
@@ -81,16 +88,27 @@ __device__ __forceinline__ float fast_rcp(float x) {
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-// x * sigmoid(k*x) with one ex2 and one rcp (MUFU), k folded with log2(e)
-__device__ __forceinline__ float x_sigmoid(float x, float k_log2e) { return x * fast_rcp(1.0f + fast_ex2(-k_log2e * x)); }
+__device__ __forceinline__ float fast_tanh(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// x * sigmoid(k*x) = h + h*tanh(k*h), h = x/2: ONE MUFU op (tanh.approx, rel. error 2^-11 — below the bf16 output
+// rounding) instead of ex2 + rcp.  The epilogue's 64 activations per lane and chunk are MUFU-throughput bound
+// (4 lanes/clk/scheduler), so this halves the dominant cost of the fc1 epilogue.
+__device__ __forceinline__ float x_sigmoid(float x, float k) {
+  const float h = 0.5f * x;
+  return fmaf(h, fast_tanh(k * h), h);
+}
 
 template <int ACT>
 __device__ __forceinline__ float apply_act(float x) {
   if (ACT == MM_ACT_QUICK_GELU) {  // x * sigmoid(1.702 x)
-    return x_sigmoid(x, 1.702f * 1.4426950408889634f);
-  } else if (ACT == MM_ACT_GELU_TANH) {  // 0.5x(1+tanh(u)) == x*sigmoid(2u), u = sqrt(2/pi)(x + 0.044715x^3)
-    const float u2 = x * (1.5957691216057308f + 0.07135481282636213f * x * x);  // 2u
-    return x * fast_rcp(1.0f + fast_ex2(-1.4426950408889634f * u2));
+    return x_sigmoid(x, 1.702f);
+  } else if (ACT == MM_ACT_GELU_TANH) {  // 0.5x(1+tanh(u)), u = sqrt(2/pi)(x + 0.044715x^3)
+    const float h = 0.5f * x;
+    const float u = x * fmaf(x * x, 0.035677408136300125f, 0.7978845608028654f);
+    return fmaf(h, fast_tanh(u), h);
   } else if (ACT == MM_ACT_GELU_ERF) {  // exact GELU; erf by Abramowitz-Stegun 7.1.26 (|err| <= 1.5e-7)
     const float ax = fabsf(x) * 0.70710678118654752440f;
     const float t = fast_rcp(fmaf(0.3275911f, ax, 1.0f));
@@ -105,7 +123,23 @@ __device__ __forceinline__ float apply_act(float x) {
   return x;
 }
 
-template <bool kGatherA, int ACT>
+// 8 values per lane x 8 lanes (ch = lane & 7) -> the total of value index `ch` ends up in this lane.
+// Halving butterfly: 7 shuffles, fixed summation order (bit-reproducible).
+__device__ __forceinline__ float butterfly8(const float (&a)[8], int ch) {
+  const bool b4 = ch & 4, b2 = ch & 2, b1 = ch & 1;
+  float u[4], v[2];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    u[i] = (b4 ? a[i + 4] : a[i]) + __shfl_xor_sync(0xffffffffu, b4 ? a[i] : a[i + 4], 4);
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+    v[i] = (b2 ? u[i + 2] : u[i]) + __shfl_xor_sync(0xffffffffu, b2 ? u[i] : u[i + 2], 2);
+  return (b1 ? v[1] : v[0]) + __shfl_xor_sync(0xffffffffu, b1 ? v[0] : v[1], 1);
+}
+
+// LN: 0 = plain epilogue, 1 = also emits row statistics (stats_out), 2 = applies the folded LayerNorm (ln_stats).
+// Compile-time, not run-time: each variant keeps the lean epilogue it needs (the epilogue is issue/i-cache bound).
+template <bool kGatherA, int ACT, int LN>
 __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
     gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                         const GemmParams p) {
@@ -228,6 +262,23 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
     uint8_t* stg = sEpi + (warp - 4) * kEpiWarpBytes;
     int as = 0;
     uint32_t aphase = 0;
+    // rv: residual segments of the current chunk — or, in LayerNorm-fold mode (no residual there), the NEXT tile's
+    // row-statistics lines, requested a whole tile ahead because global-load latency is fully exposed in this
+    // 2-warps-per-scheduler epilogue.
+    int4 rv[8];
+    constexpr bool fold_mode = !kGatherA && LN == 2;
+    const int ln_slots = ((((p.K + 63) >> 6) + 15) >> 4) << 4;
+    auto load_stats = [&](int tile) {
+      const int mb = (tile / p.tiles_n) * BM + q * 32 + (lane >> 3);
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int gm = mb + it * 4;
+        rv[it] = make_int4(0, 0, 0, 0);
+        if (tile < num_tiles && gm < p.M)
+          rv[it] = __ldg(reinterpret_cast<const int4*>(p.ln_stats + (int64_t)gm * ln_slots) + (lane & 7));
+      }
+    };
+    if (fold_mode) load_stats(blockIdx.x);
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       const int m0 = (t / p.tiles_n) * BM, n0 = (t % p.tiles_n) * BN;
       // destination row of this lane's GEMM row
@@ -242,6 +293,37 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
         } else {
           my_out = my_m;
         }
+      }
+      // folded LayerNorm: this lane's row statistics from the producer GEMM's per-chunk partials (fixed order)
+      float ln_rstd = 1.f;
+      if (fold_mode) {
+        const int slots = ln_slots;
+        float4 sv[8];   // this tile's statistics lines: requested during the previous tile (first tile: above)
+#pragma unroll
+        for (int it = 0; it < 8; ++it)
+          sv[it] = make_float4(__int_as_float(rv[it].x), __int_as_float(rv[it].y), __int_as_float(rv[it].z),
+                               __int_as_float(rv[it].w));
+        float ps[8], pq[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          ps[it] = sv[it].x + sv[it].z, pq[it] = sv[it].y + sv[it].w;
+          const int gm = m0 + q * 32 + it * 4 + (lane >> 3);
+          if (slots > 16 && gm < p.M) {   // K > 1024 (SigLIP): further 128-byte groups
+            const float4* sp = reinterpret_cast<const float4*>(p.ln_stats + (int64_t)gm * slots) + (lane & 7);
+            for (int gi = 1; gi < (slots >> 4); ++gi) {
+              const float4 v = __ldg(sp + gi * 8);
+              ps[it] += v.x + v.z;
+              pq[it] += v.y + v.w;
+            }
+          }
+        }
+        const float ts = butterfly8(ps, lane & 7), tq = butterfly8(pq, lane & 7);  // row (lane&7)*4 + (lane>>3)
+        const int src = ((lane & 3) << 3) | (lane >> 2);                            // lane that holds row `lane`
+        const float s1 = __shfl_sync(0xffffffffu, ts, src), s2 = __shfl_sync(0xffffffffu, tq, src);
+        const float mean = s1 * p.ln_inv_k;
+        const float var = fmaxf(s2 * p.ln_inv_k - mean * mean, 0.f);
+        ln_rstd = rsqrtf(var + p.ln_eps);
+        load_stats(t + (int)gridDim.x);   // rv is free again: request the next tile's lines now
       }
       mbar_wait(&tail->tmem_full[as], aphase);
       tc_fence_after();
@@ -264,14 +346,13 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
         const int ch = lane & 7;
         const int col = col0 + ch * 8;
         int out_rows[8];
-        int4 rv[8];
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
           const int r = it * 4 + (lane >> 3);
           out_rows[it] = __shfl_sync(0xffffffffu, my_out, r);
           if (col >= p.N) out_rows[it] = -1;
-          rv[it] = make_int4(0, 0, 0, 0);
-          if (p.residual && out_rows[it] >= 0) {
+          if (!fold_mode) rv[it] = make_int4(0, 0, 0, 0);
+          if (!fold_mode && p.residual && out_rows[it] >= 0) {
             const int gm = m0 + q * 32 + r;
             const int64_t rr = (int64_t)((p.res_mod > 0 ? gm % p.res_mod : gm) + p.res_row_off);
             rv[it] = __ldg(reinterpret_cast<const int4*>(p.residual + rr * p.ldr + col));
@@ -279,6 +360,8 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
         }
         tc_wait_ld();
         // bias + activation in fp32, on the bf16-rounded pre-activation (nn.Linear output rounding)
+        constexpr bool fold = fold_mode;
+        const uint64_t rstd2 = f32x2(ln_rstd, ln_rstd);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const uint32_t bw[4] = {(uint32_t)bv[j].x, (uint32_t)bv[j].y, (uint32_t)bv[j].z, (uint32_t)bv[j].w};
@@ -286,8 +369,11 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
           uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            float x0 = __uint_as_float(acc[j * 8 + 2 * e]) + bf16_lo(bw[e]);
-            float x1 = __uint_as_float(acc[j * 8 + 2 * e + 1]) + bf16_hi(bw[e]);
+            const uint64_t a2 = f32x2(__uint_as_float(acc[j * 8 + 2 * e]), __uint_as_float(acc[j * 8 + 2 * e + 1]));
+            const uint64_t b2 = f32x2(bf16_lo(bw[e]), bf16_hi(bw[e]));
+            const uint64_t x2 = fold ? fma_f32x2(rstd2, a2, b2) : add_f32x2(a2, b2);  // fold: rstd*(x·W''ᵀ) + b'
+            float x0, x1;
+            f32x2_unpack(x2, x0, x1);
             if (ACT != MM_ACT_NONE) {
               const uint32_t r = pack_bf16x2(x0, x1);
               x0 = apply_act<ACT>(bf16_lo(r));
@@ -299,19 +385,44 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
         }
         __syncwarp();
         // coalesced phase: 8 lanes cover one 128-B row segment, 4 rows per instruction
+        constexpr bool want_stats = !kGatherA && LN == 1;
+        float st_s[8], st_q[8];
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
           const int r = it * 4 + (lane >> 3);
           uint4 v = *reinterpret_cast<const uint4*>(stg + r * 128 + ((ch ^ (r & 7)) << 4));
+          st_s[it] = 0.f, st_q[it] = 0.f;
           if (out_rows[it] >= 0) {
-            if (p.residual) {
-              v.x = pack_bf16x2(bf16_lo(v.x) + bf16_lo((uint32_t)rv[it].x), bf16_hi(v.x) + bf16_hi((uint32_t)rv[it].x));
-              v.y = pack_bf16x2(bf16_lo(v.y) + bf16_lo((uint32_t)rv[it].y), bf16_hi(v.y) + bf16_hi((uint32_t)rv[it].y));
-              v.z = pack_bf16x2(bf16_lo(v.z) + bf16_lo((uint32_t)rv[it].z), bf16_hi(v.z) + bf16_hi((uint32_t)rv[it].z));
-              v.w = pack_bf16x2(bf16_lo(v.w) + bf16_lo((uint32_t)rv[it].w), bf16_hi(v.w) + bf16_hi((uint32_t)rv[it].w));
+            if (!fold_mode && p.residual) {  // bf16 + bf16, one rounding (HADD2.BF16)
+              v.x = add_bf16x2(v.x, (uint32_t)rv[it].x);
+              v.y = add_bf16x2(v.y, (uint32_t)rv[it].y);
+              v.z = add_bf16x2(v.z, (uint32_t)rv[it].z);
+              v.w = add_bf16x2(v.w, (uint32_t)rv[it].w);
             }
             *reinterpret_cast<uint4*>(p.C + (int64_t)out_rows[it] * p.ldc + col) = v;
+            if (want_stats) {  // statistics of the values as stored (bf16-rounded), fp32, two lanes per instruction
+              const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
+              uint64_t s2 = 0ull, q2 = 0ull;
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const uint64_t ab = f32x2(bf16_lo(vw[e]), bf16_hi(vw[e]));
+                s2 = add_f32x2(s2, ab);
+                q2 = fma_f32x2(ab, ab, q2);
+              }
+              float a, b;
+              f32x2_unpack(s2, a, b);
+              st_s[it] = a + b;
+              f32x2_unpack(q2, a, b);
+              st_q[it] = a + b;
+            }
           }
+        }
+        if (want_stats) {
+          const float ts = butterfly8(st_s, ch), tq = butterfly8(st_q, ch);
+          // this lane now owns row it = ch of its 4-row group
+          const int orow = __shfl_sync(0xffffffffu, my_out, ch * 4 + (lane >> 3));
+          if (orow >= 0)
+            p.stats_out[(int64_t)orow * (((((p.N + 63) >> 6) + 15) >> 4) << 4) + (col0 >> 6)] = make_float2(ts, tq);
         }
         __syncwarp();
       }
@@ -463,14 +574,14 @@ int make_tmap_3d_sw32(CUtensorMap* tm, const void* ptr, int64_t d0, int64_t d1, 
   return MM_OK;
 }
 
-template <bool kGatherA, int ACT>
+template <bool kGatherA, int ACT, int LN = 0>
 static int launch_gemm_inst(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
   using Cfg = GemmCfg<kGatherA>;
   static bool attr_set[64] = {false};
   int dev = 0;
   MM_CUDA_CHECK(cudaGetDevice(&dev));
   if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-    MM_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_tn_kernel<kGatherA, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    MM_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_tn_kernel<kGatherA, ACT, LN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        Cfg::kSmemBytes));
     attr_set[dev] = true;
   }
@@ -479,12 +590,25 @@ static int launch_gemm_inst(const CUtensorMap& tmA, const CUtensorMap& tmB, Gemm
   const int tiles = p.tiles_m * p.tiles_n;
   const int sms = sm_count();
   const int grid = tiles < sms ? tiles : sms;
-  gemm_bf16_tn_kernel<kGatherA, ACT><<<grid, Cfg::kThreads, Cfg::kSmemBytes, st>>>(tmA, tmB, p);
+  gemm_bf16_tn_kernel<kGatherA, ACT, LN><<<grid, Cfg::kThreads, Cfg::kSmemBytes, st>>>(tmA, tmB, p);
   MM_CUDA_CHECK(cudaGetLastError());
   return MM_OK;
 }
 
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
+  if (p.ln_stats) {   // consumer of a folded LayerNorm (QKV: no activation; fc1: QuickGELU / tanh-GELU)
+    if (p.stats_out) return MM_ERR_BAD_ARG;
+    switch (p.act) {
+      case MM_ACT_NONE: return launch_gemm_inst<false, MM_ACT_NONE, 2>(tmA, tmB, p, st);
+      case MM_ACT_QUICK_GELU: return launch_gemm_inst<false, MM_ACT_QUICK_GELU, 2>(tmA, tmB, p, st);
+      case MM_ACT_GELU_TANH: return launch_gemm_inst<false, MM_ACT_GELU_TANH, 2>(tmA, tmB, p, st);
+    }
+    return MM_ERR_BAD_ARG;
+  }
+  if (p.stats_out) {  // producer of row statistics (out-proj / fc2: bias + residual, no activation)
+    if (p.act != MM_ACT_NONE) return MM_ERR_BAD_ARG;
+    return launch_gemm_inst<false, MM_ACT_NONE, 1>(tmA, tmB, p, st);
+  }
   switch (p.act) {
     case MM_ACT_NONE: return launch_gemm_inst<false, MM_ACT_NONE>(tmA, tmB, p, st);
     case MM_ACT_QUICK_GELU: return launch_gemm_inst<false, MM_ACT_QUICK_GELU>(tmA, tmB, p, st);
@@ -500,10 +624,10 @@ using namespace mm;
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-extern "C" int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias, void* C,
-                                int64_t ldc, int64_t M, int64_t N, int64_t K, int act, const void* residual,
-                                int64_t ldr, int64_t res_mod, int64_t res_row_off, const int32_t* out_row_map,
-                                int64_t n_out_rows, void* stream) {
+static int gemm_entry(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias, void* C, int64_t ldc,
+                      int64_t M, int64_t N, int64_t K, int act, const void* residual, int64_t ldr, int64_t res_mod,
+                      int64_t res_row_off, const int32_t* out_row_map, int64_t n_out_rows, void* stats_out,
+                      const void* ln_stats, float ln_eps, void* stream) {
   if (M < 0 || N <= 0 || K <= 0 || M > INT32_MAX / 2 || N > INT32_MAX / 2 || K > INT32_MAX / 2) return MM_ERR_BAD_ARG;
   if (M == 0) return MM_OK;
   if (!A || !W || !C) return MM_ERR_BAD_ARG;
@@ -529,7 +653,32 @@ extern "C" int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64
   p.M = (int)M, p.N = (int)N, p.K = (int)K;
   p.res_mod = (int)res_mod, p.res_row_off = (int)res_row_off;
   p.act = act;
+  if (ln_stats && residual) return MM_ERR_BAD_ARG;  // the epilogue's residual registers carry the statistics
+  if (!aligned16(ln_stats) || !aligned16(stats_out))
+    return MM_ERR_BAD_ARG;
+  p.stats_out = reinterpret_cast<float2*>(stats_out);
+  p.ln_stats = reinterpret_cast<const float2*>(ln_stats);
+  p.ln_eps = ln_eps;
+  p.ln_inv_k = 1.0f / (float)K;
   return launch_gemm(tmA, tmB, p, reinterpret_cast<cudaStream_t>(stream));
+}
+
+extern "C" int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias, void* C,
+                                int64_t ldc, int64_t M, int64_t N, int64_t K, int act, const void* residual,
+                                int64_t ldr, int64_t res_mod, int64_t res_row_off, const int32_t* out_row_map,
+                                int64_t n_out_rows, void* stream) {
+  return gemm_entry(A, lda, W, ldw, bias, C, ldc, M, N, K, act, residual, ldr, res_mod, res_row_off, out_row_map,
+                    n_out_rows, nullptr, nullptr, 0.f, stream);
+}
+
+extern "C" int64_t mm_gemm_row_stats_slots(int64_t N) { return N > 0 ? ((N + 63) / 64 + 15) / 16 * 16 : -1; }
+
+extern "C" int mm_gemm_ln_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias, void* C,
+                                   int64_t ldc, int64_t M, int64_t N, int64_t K, int act, const void* residual,
+                                   int64_t ldr, const int32_t* out_row_map, int64_t n_out_rows, void* stats_out,
+                                   const void* ln_stats, float ln_eps, void* stream) {
+  return gemm_entry(A, lda, W, ldw, bias, C, ldc, M, N, K, act, residual, ldr, 0, 0, out_row_map, n_out_rows, stats_out,
+                    ln_stats, ln_eps, stream);
 }
 
 extern "C" int mm_patch_embed(const void* pixels, int pixel_dtype, int64_t B, int64_t img, int64_t patch,

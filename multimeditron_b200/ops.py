@@ -238,6 +238,67 @@ def gemm_bias_act(a: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = 
     return out
 
 
+def gemm_ln_bias_act(a: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None = None, act: int = ACT_NONE,
+                     residual: torch.Tensor | None = None, out: torch.Tensor | None = None,
+                     out_row_map: torch.Tensor | None = None, stats_out: torch.Tensor | None = None,
+                     ln_stats: torch.Tensor | None = None, eps: float = 1e-5) -> torch.Tensor:
+    """mm_gemm_ln_bias_act (include/mm_b200.h): GEMM that emits row statistics of what it stores (stats_out
+    fp32 [rows, slots, 2], zero-initialised once) and/or consumes them (ln_stats) to apply a folded LayerNorm to
+    its A operand; in that case (w, bias) must come from `fold_layernorm`."""
+    _cuda(a, w, bias, residual, out, out_row_map, stats_out, ln_stats)
+    lib = _lib.load()
+    assert a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and a.dim() == 2 and w.dim() == 2
+    assert a.stride(1) == 1 and w.stride(1) == 1
+    M, K = a.shape
+    N = w.shape[0]
+    assert w.shape[1] == K
+    if out is None:
+        assert out_row_map is None
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=a.device)
+    assert out.dtype == torch.bfloat16 and out.stride(-1) == 1
+    ldc = out.stride(-2) if out.dim() >= 2 else N
+    ldr = residual.stride(-2) if residual is not None else 0
+    n_out_rows = (out.numel() // N if out.is_contiguous() else out.shape[0]) if out_row_map is not None else 0
+    if stats_out is not None:
+        rows = n_out_rows if out_row_map is not None else M
+        assert stats_out.dtype == torch.float32 and stats_out.is_contiguous()
+        assert stats_out.numel() >= rows * row_stats_slots(N) * 2
+    if ln_stats is not None:
+        assert ln_stats.dtype == torch.float32 and ln_stats.is_contiguous()
+        assert ln_stats.numel() >= M * row_stats_slots(K) * 2
+    with _timed("mm_gemm_bias_act", 2.0 * M * N * K):
+        rc = lib.mm_gemm_ln_bias_act(_ptr(a), a.stride(0), _ptr(w), w.stride(0), _ptr(bias), _ptr(out), ldc, M, N, K,
+                                     int(act), _ptr(residual), ldr, _ptr(out_row_map), n_out_rows, _ptr(stats_out),
+                                     _ptr(ln_stats), float(eps), _stream())
+    _check(rc, "mm_gemm_ln_bias_act")
+    return out
+
+
+def row_stats_slots(n: int) -> int:
+    return int(_lib.load().mm_gemm_row_stats_slots(n))
+
+
+def fold_layernorm(w: torch.Tensor, bias: torch.Tensor | None, gamma: torch.Tensor, beta: torch.Tensor):
+    """(W'', b') for the consumer side of mm_gemm_ln_bias_act.
+    W'' = gamma*W with each row re-centred to zero sum, rounded to bf16 with error feedback along k (sigma-delta), so
+    the bf16 row sums stay within half an ulp of zero and the LayerNorm mean term cancels inside the MMA;
+    b' = bias + W @ beta, rounded to bf16."""
+    wf = w.float()
+    wg = wf * gamma.float()[None, :]
+    wg = wg - wg.mean(1, keepdim=True)
+    q = torch.empty_like(wg, dtype=torch.bfloat16)
+    err = torch.zeros(wg.shape[0], dtype=torch.float32, device=wg.device)
+    for k in range(wg.shape[1]):          # load-time only
+        t = wg[:, k] + err
+        qk = t.to(torch.bfloat16)
+        q[:, k] = qk
+        err = t - qk.float()
+    b = wf @ beta.float()
+    if bias is not None:
+        b = b + bias.float()
+    return q.contiguous(), b.to(torch.bfloat16).contiguous()
+
+
 def patch_embed(pixels: torch.Tensor, weight_padded: torch.Tensor, conv_bias, pos_emb: torch.Tensor, cls,
                 patch: int, out: torch.Tensor | None = None) -> torch.Tensor:
     """pixels [B,3,img,img] fp32/bf16; weight_padded [D, Kpad] bf16 (zero padded) -> [B,T,D] bf16."""

@@ -2,15 +2,19 @@
 
 `TowerWeights` packs a reference state dict (feature_extractor.vision_model.* / projector.projection.{0,2,4}.*)
 once into the layouts the kernels want (fused [3D,D] QKV weight, zero-padded [D,Kpad] patch weight, bf16).
-`TowerRunner.forward` issues, per encoder layer, 7 kernel launches on the current stream:
-    LN1 -> GEMM(qkv,+bias) -> attention -> GEMM(out,+bias,+residual) -> LN2 -> GEMM(fc1,+bias,act) ->
-    GEMM(fc2,+bias,+residual)
+`TowerRunner.forward` issues, per encoder layer, 5 kernel launches on the current stream:
+    GEMM(qkv, LN1 folded) -> attention -> GEMM(out,+bias,+residual, emits row stats) -> GEMM(fc1, LN2 folded, act) ->
+    GEMM(fc2,+bias,+residual, emits row stats)
+(the two LayerNorms are folded into the consuming GEMMs: statistics come out of the producing GEMM's epilogue, the
+normalisation is applied in the consumer's epilogue — mm_gemm_ln_bias_act; only layer 0's LN1 is a separate launch),
 then the 3 projector GEMMs (bias+erf-GELU epilogues); the last one can scatter its rows straight into
 inputs_embeds (splice fused into the epilogue).  No host sync anywhere on the path.
 
 Reference: image_modality.py:130-137; HF:models/clip/modeling_clip.py:667-692; projectors/mlp.py:33-39.
 """
 from __future__ import annotations
+
+import os
 
 import torch
 
@@ -22,6 +26,10 @@ VM = "feature_extractor.vision_model."
 
 def _bf(t: torch.Tensor, device) -> torch.Tensor:
     return t.detach().to(device=device, dtype=torch.bfloat16).contiguous()
+
+
+# MM_B200_FOLD_LN=0 keeps the separate LayerNorm launches (A/B switch for tools and tests)
+FOLD_LN = os.environ.get("MM_B200_FOLD_LN", "1") != "0"
 
 
 class TowerWeights:
@@ -74,6 +82,15 @@ class TowerWeights:
                 w1=g("mlp.fc1.weight"), b1=g("mlp.fc1.bias"),
                 w2=g("mlp.fc2.weight"), b2=g("mlp.fc2.bias"),
             ))
+            if FOLD_LN:
+                # LayerNorm folded into the consuming GEMM (mm_gemm_ln_bias_act): zero-row-sum W'' = gamma*W, b' = b + W beta.
+                # LN1 of layer 0 keeps the LayerNorm kernel (its input comes from pre-LN / patch-embed, no statistics).
+                Lw = self.layers[-1]
+                Lw["w1_f"], Lw["b1_f"] = ops.fold_layernorm(Lw["w1"], Lw["b1"], *Lw["ln2"])
+                if i > 0:
+                    Lw["wqkv_f"], Lw["bqkv_f"] = ops.fold_layernorm(Lw["wqkv"], Lw["bqkv"], *Lw["ln1"])
+                    del Lw["wqkv"], Lw["bqkv"]
+                del Lw["w1"], Lw["b1"]
         self.proj = None
         if with_projector:
             self.proj = ProjectorWeights(sd, dev, proj_prefix)
@@ -107,7 +124,7 @@ class TowerRunner:
             c, dev = self.cfg, self.w.device
             M, D, I = B * c.num_tokens, c.hidden_size, c.intermediate_size
             e = lambda *s: torch.empty(*s, dtype=torch.bfloat16, device=dev)  # noqa: E731
-            ws = dict(x=e(M, D), h=e(M, D), qkv=e(M, 3 * c.num_attention_heads * self.w.head_stride), attn=e(M, D), mlp=e(M, I), feats=e(B * c.num_patches, D))
+            ws = dict(stats=torch.zeros(M, ops.row_stats_slots(D), 2, dtype=torch.float32, device=dev), x=e(M, D), h=e(M, D), qkv=e(M, 3 * c.num_attention_heads * self.w.head_stride), attn=e(M, D), mlp=e(M, I), feats=e(B * c.num_patches, D))
             if c.has_cls:  # GEMM row m (token) -> compact feature row, CLS rows dropped (image_modality.py:133)
                 m = torch.arange(M, device=dev, dtype=torch.int64)
                 t = m % c.num_tokens
@@ -142,14 +159,25 @@ class TowerRunner:
         if w.pre_ln is not None:
             ops.layernorm(x, w.pre_ln[0], w.pre_ln[1], c.layer_norm_eps, out=x)
         n_layers = len(w.layers)
+        stats, eps = ws["stats"], c.layer_norm_eps
         for i, L in enumerate(w.layers):
-            ops.layernorm(x, L["ln1"][0], L["ln1"][1], c.layer_norm_eps, out=h)
-            ops.gemm_bias_act(h, L["wqkv"], L["bqkv"], out=qkv)
-            ops.attention_fwd(qkv, B, T, nh, hd, hd ** -0.5, out=attn)
-            ops.gemm_bias_act(attn, L["wo"], L["bo"], residual=x, out=x)
-            ops.layernorm(x, L["ln2"][0], L["ln2"][1], c.layer_norm_eps, out=h)
-            ops.gemm_bias_act(h, L["w1"], L["b1"], act=act, out=mlp)
             last = i == n_layers - 1
+            if "wqkv_f" in L:   # LN1 folded: statistics of x came out of the previous layer's fc2 epilogue
+                ops.gemm_ln_bias_act(x, L["wqkv_f"], L["bqkv_f"], out=qkv, ln_stats=stats, eps=eps)
+            else:
+                ops.layernorm(x, L["ln1"][0], L["ln1"][1], eps, out=h)
+                ops.gemm_bias_act(h, L["wqkv"], L["bqkv"], out=qkv)
+            ops.attention_fwd(qkv, B, T, nh, hd, hd ** -0.5, out=attn)
+            if "w1_f" in L:     # out-proj emits the row statistics LN2 needs; fc1 applies LN2 in its epilogue
+                ops.gemm_ln_bias_act(attn, L["wo"], L["bo"], residual=x, out=x, stats_out=stats)
+                ops.gemm_ln_bias_act(x, L["w1_f"], L["b1_f"], act=act, out=mlp, ln_stats=stats, eps=eps)
+                if not last:
+                    ops.gemm_ln_bias_act(mlp, L["w2"], L["b2"], residual=x, out=x, stats_out=stats)
+                    continue
+            else:
+                ops.gemm_bias_act(attn, L["wo"], L["bo"], residual=x, out=x)
+                ops.layernorm(x, L["ln2"][0], L["ln2"][1], eps, out=h)
+                ops.gemm_bias_act(h, L["w1"], L["b1"], act=act, out=mlp)
             if last and c.has_cls:
                 # last fc2 writes the compact [B*P, D] feature matrix directly (CLS rows never stored)
                 rmap, dst = ws["drop_cls"], feats

@@ -97,6 +97,51 @@ def test_gemm_modular_residual_and_strided_output():
     assert not big[:, :N].any()
 
 
+@pytest.mark.parametrize("M,D,N,act,eps,shift", [
+    (300, 128, 256, 1, 1e-5, 0.0),        # tiny tower width, one stats slot pair
+    (1000, 1024, 3072, 0, 1e-5, 0.0),     # CLIP-L QKV
+    (577, 1024, 4096, 1, 1e-5, 3.0),      # CLIP-L fc1 + QuickGELU, rows with a large mean (cancellation in acc - mean*c)
+    (729, 1152, 4304, 3, 1e-6, 0.5),      # SigLIP fc1 + tanh-GELU, 18 slots
+    (130, 144, 480, 0, 1e-6, 0.0),        # widths that are not multiples of 64/128: partial last chunk
+])
+def test_gemm_layernorm_fold(M, D, N, act, eps, shift):
+    """Producer GEMM (+bias +residual) emits per-chunk row statistics; consumer GEMM applies LayerNorm from them.
+    Compared with fp32 torch: LN(x) @ W.T + b (x = what the producer stored)."""
+    g0 = torch.Generator().manual_seed(M + N)
+    a = torch.randn(M, 256, generator=g0).bfloat16().to(DEV)
+    wo = (torch.randn(D, 256, generator=g0) * 0.05).bfloat16().to(DEV)
+    bo = (torch.randn(D, generator=g0) * 0.1).bfloat16().to(DEV)
+    res = (torch.randn(M, D, generator=g0) * (1.0 + 4.0 * (torch.rand(1, D, generator=g0) > 0.97)) + shift).bfloat16().to(DEV)
+    stats = torch.zeros(M, ops.row_stats_slots(D), 2, device=DEV)   # contract: zero-initialised once
+    assert ops.row_stats_slots(D) % 16 == 0
+    x = ops.gemm_ln_bias_act(a, wo, bo, residual=res, stats_out=stats)
+    x_plain = ops.gemm_bias_act(a, wo, bo, residual=res)
+    assert torch.equal(x, x_plain)                               # emitting statistics must not change the output
+    xs = x.float()
+    # statistics: chunk sums of the stored bf16 values
+    pad = (-D) % 64
+    xp = torch.nn.functional.pad(xs, (0, pad)).view(M, -1, 64)
+    nc = xp.shape[1]
+    assert torch.allclose(stats[:, :nc, 0], xp.sum(-1), rtol=1e-5, atol=1e-3)
+    assert torch.allclose(stats[:, :nc, 1], (xp * xp).sum(-1), rtol=1e-5, atol=1e-3)
+    assert (stats[:, nc:] == 0).all()
+    gamma = (1 + 0.1 * torch.randn(D, generator=g0)).bfloat16().to(DEV)
+    beta = (0.1 * torch.randn(D, generator=g0)).bfloat16().to(DEV)
+    w = (torch.randn(N, D, generator=g0) * 0.02).bfloat16().to(DEV)
+    b = (torch.randn(N, generator=g0) * 0.02).bfloat16().to(DEV)
+    wf, bf = ops.fold_layernorm(w, b, gamma, beta)
+    y = ops.gemm_ln_bias_act(x, wf, bf, act=act, ln_stats=stats, eps=eps)
+    h = F.layer_norm(xs, (D,), gamma.float(), beta.float(), eps)
+    ref = h @ w.float().T + b.float()
+    ref = {0: lambda t: t, 1: lambda t: t * torch.sigmoid(1.702 * t), 3: lambda t: F.gelu(t, approximate="tanh")}[act](ref)
+    close(y, ref)
+    # and it must agree with the unfolded two-kernel path at bf16 level
+    y2 = ops.gemm_bias_act(ops.layernorm(x, gamma, beta, eps), w, b, act=act)
+    close(y, y2.float())
+    y_again = ops.gemm_ln_bias_act(x, wf, bf, act=act, ln_stats=stats, eps=eps)
+    assert torch.equal(y, y_again)                               # fixed summation order: bit-reproducible
+
+
 def test_gemm_rejects_bad_arguments():
     a = torch.zeros(16, 12, device=DEV).bfloat16()   # K % 8 != 0
     w = torch.zeros(16, 12, device=DEV).bfloat16()
