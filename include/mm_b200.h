@@ -148,13 +148,13 @@ int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, con
  *     LN(x)·Wᵀ + b  =  rstd · (x·W''ᵀ) + b',    W'' = gamma ⊙ W with every row re-centred to sum to zero
  *                                               (so the −mean·Σ_k W'' term vanishes inside the MMA),
  *                                               b'_n = b_n + Σ_k beta_k·W[n,k]
- *   producer side  stats_out != NULL: after bias/act/residual, every stored row also emits, per 64-column chunk,
- *                  (Σ v, Σ v²) of the bf16 values it stored: stats_out [rows of C][mm_gemm_row_stats_slots(N)] float2
- *                  (slot count rounded up to 16 = whole 128-byte lines; the buffer must be ZERO-initialised once,
- *                  unused slots are never written).
+ *   producer side  stats_out != NULL (act must be NONE): after bias/residual, every stored row also emits, per 128
+ *                  output columns, (Σ v, Σ v²) of the bf16 values it stored: stats_out [rows of C][16] float2 — one
+ *                  128-byte line per row, N <= 2048 (mm_gemm_row_stats_slots(N) = 16, or -1 when N is too wide).
+ *                  The buffer must be ZERO-initialised once; slots beyond ceil(N/128) are never written.
  *   consumer side  ln_stats != NULL: A is the RAW residual stream x, W is W'' and `bias` is b' (both packed once at
  *                  load time, bf16; W'' is rounded with error feedback along k so that its bf16 row sums stay ~0),
- *                  the epilogue rebuilds rstd of row m from ln_stats [M][mm_gemm_row_stats_slots(K)] (summed in a
+ *                  the epilogue rebuilds rstd of row m from ln_stats [M][16] float2 (no residual in this mode; summed in a
  *                  fixed order: bit-reproducible) and forms bf16(rstd·acc + b').  Rounding then follows
  *                  mm_gemm_bias_act.
  * Numerics: the reference rounds LN(x) to bf16 before the GEMM; here gamma ⊙ W is rounded to bf16 instead and

@@ -28,6 +28,7 @@ constexpr int kEpiWarpBytes = 32 * 128;    // 32 rows x 64 bf16
 constexpr int kTmemCols = 512;
 constexpr int kKTableMax = 3072 + 64;  // patch-embed k -> pixel offset table (ints)
 
+constexpr int kStatSlots = 16;  // row-statistics slots per row: one 128-byte line, one slot per 128 output columns
 constexpr int kMaxStages = 4;
 struct GemmSmemTail {
   uint64_t full[kMaxStages];
@@ -137,7 +138,8 @@ __device__ __forceinline__ float butterfly8(const float (&a)[8], int ch) {
   return (b1 ? v[1] : v[0]) + __shfl_xor_sync(0xffffffffu, b1 ? v[0] : v[1], 1);
 }
 
-// LN: 0 = plain epilogue, 1 = also emits row statistics (stats_out), 2 = applies the folded LayerNorm (ln_stats).
+// LN: 0 = plain epilogue, 1 = also emits row statistics (stats_out), 2 = applies the folded LayerNorm (ln_stats),
+// 3 = plain with a modular residual row (res_mod > 0).
 // Compile-time, not run-time: each variant keeps the lean epilogue it needs (the epilogue is issue/i-cache bound).
 template <bool kGatherA, int ACT, int LN>
 __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
@@ -267,7 +269,7 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
     // 2-warps-per-scheduler epilogue.
     int4 rv[8];
     constexpr bool fold_mode = !kGatherA && LN == 2;
-    const int ln_slots = ((((p.K + 63) >> 6) + 15) >> 4) << 4;
+    constexpr int ln_slots = kStatSlots;
     auto load_stats = [&](int tile) {
       const int mb = (tile / p.tiles_n) * BM + q * 32 + (lane >> 3);
 #pragma unroll
@@ -297,7 +299,6 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
       // folded LayerNorm: this lane's row statistics from the producer GEMM's per-chunk partials (fixed order)
       float ln_rstd = 1.f;
       if (fold_mode) {
-        const int slots = ln_slots;
         float4 sv[8];   // this tile's statistics lines: requested during the previous tile (first tile: above)
 #pragma unroll
         for (int it = 0; it < 8; ++it)
@@ -307,15 +308,6 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
           ps[it] = sv[it].x + sv[it].z, pq[it] = sv[it].y + sv[it].w;
-          const int gm = m0 + q * 32 + it * 4 + (lane >> 3);
-          if (slots > 16 && gm < p.M) {   // K > 1024 (SigLIP): further 128-byte groups
-            const float4* sp = reinterpret_cast<const float4*>(p.ln_stats + (int64_t)gm * slots) + (lane & 7);
-            for (int gi = 1; gi < (slots >> 4); ++gi) {
-              const float4 v = __ldg(sp + gi * 8);
-              ps[it] += v.x + v.z;
-              pq[it] += v.y + v.w;
-            }
-          }
         }
         const float ts = butterfly8(ps, lane & 7), tq = butterfly8(pq, lane & 7);  // row (lane&7)*4 + (lane>>3)
         const int src = ((lane & 3) << 3) | (lane >> 2);                            // lane that holds row `lane`
@@ -328,6 +320,7 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
       mbar_wait(&tail->tmem_full[as], aphase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
+      float tile_ts = 0.f, tile_tq = 0.f;   // LN == 1: this warp's 128-column group of row statistics
 #pragma unroll 1
       for (int cc = 0; cc < Cfg::kChunksPerWarp; ++cc) {
         const int c = half * Cfg::kChunksPerWarp + cc;
@@ -354,7 +347,9 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
           if (!fold_mode) rv[it] = make_int4(0, 0, 0, 0);
           if (!fold_mode && p.residual && out_rows[it] >= 0) {
             const int gm = m0 + q * 32 + r;
-            const int64_t rr = (int64_t)((p.res_mod > 0 ? gm % p.res_mod : gm) + p.res_row_off);
+            // the modular row (positional embeddings) costs an integer division per row: compiled only where used
+            constexpr bool kModRes = kGatherA || LN == 3;
+            const int64_t rr = (int64_t)((kModRes && p.res_mod > 0 ? gm % p.res_mod : gm) + p.res_row_off);
             rv[it] = __ldg(reinterpret_cast<const int4*>(p.residual + rr * p.ldr + col));
           }
         }
@@ -418,13 +413,16 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
           }
         }
         if (want_stats) {
-          const float ts = butterfly8(st_s, ch), tq = butterfly8(st_q, ch);
-          // this lane now owns row it = ch of its 4-row group
-          const int orow = __shfl_sync(0xffffffffu, my_out, ch * 4 + (lane >> 3));
-          if (orow >= 0)
-            p.stats_out[(int64_t)orow * (((((p.N + 63) >> 6) + 15) >> 4) << 4) + (col0 >> 6)] = make_float2(ts, tq);
+          // after the butterfly this lane owns row (ch*4 + lane/8) of the warp's 32 rows; chunks add in a fixed order
+          tile_ts += butterfly8(st_s, ch);
+          tile_tq += butterfly8(st_q, ch);
         }
         __syncwarp();
+      }
+      if (!kGatherA && LN == 1) {
+        const int gcol = n0 + half * (BN / 2);
+        const int orow = __shfl_sync(0xffffffffu, my_out, (lane & 7) * 4 + (lane >> 3));
+        if (orow >= 0 && gcol < p.N) p.stats_out[(int64_t)orow * kStatSlots + (gcol >> 7)] = make_float2(tile_ts, tile_tq);
       }
       // all TMEM reads of this accumulator stage are complete (tc_wait_ld above)
       tc_fence_before();
@@ -609,6 +607,10 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParam
     if (p.act != MM_ACT_NONE) return MM_ERR_BAD_ARG;
     return launch_gemm_inst<false, MM_ACT_NONE, 1>(tmA, tmB, p, st);
   }
+  if (p.res_mod > 0) {
+    if (p.act != MM_ACT_NONE) return MM_ERR_BAD_ARG;
+    return launch_gemm_inst<false, MM_ACT_NONE, 3>(tmA, tmB, p, st);
+  }
   switch (p.act) {
     case MM_ACT_NONE: return launch_gemm_inst<false, MM_ACT_NONE>(tmA, tmB, p, st);
     case MM_ACT_QUICK_GELU: return launch_gemm_inst<false, MM_ACT_QUICK_GELU>(tmA, tmB, p, st);
@@ -654,6 +656,7 @@ static int gemm_entry(const void* A, int64_t lda, const void* W, int64_t ldw, co
   p.res_mod = (int)res_mod, p.res_row_off = (int)res_row_off;
   p.act = act;
   if (ln_stats && residual) return MM_ERR_BAD_ARG;  // the epilogue's residual registers carry the statistics
+  if ((ln_stats && K > 128 * kStatSlots) || (stats_out && N > 128 * kStatSlots)) return MM_ERR_BAD_ARG;
   if (!aligned16(ln_stats) || !aligned16(stats_out))
     return MM_ERR_BAD_ARG;
   p.stats_out = reinterpret_cast<float2*>(stats_out);
@@ -671,7 +674,7 @@ extern "C" int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64
                     n_out_rows, nullptr, nullptr, 0.f, stream);
 }
 
-extern "C" int64_t mm_gemm_row_stats_slots(int64_t N) { return N > 0 ? ((N + 63) / 64 + 15) / 16 * 16 : -1; }
+extern "C" int64_t mm_gemm_row_stats_slots(int64_t N) { return (N > 0 && N <= 128 * kStatSlots) ? kStatSlots : -1; }
 
 extern "C" int mm_gemm_ln_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias, void* C,
                                    int64_t ldc, int64_t M, int64_t N, int64_t K, int act, const void* residual,
