@@ -37,9 +37,9 @@ WORKLOADS = {
 }
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` capture of this command at
-# cfg2 B=256 (profiles/r01c_ncu_full_summary.txt): GEMM = mean over one encoder layer's four launches
-# (fc2 1.807, qkv 1.161, out-proj 0.867, fc1 1.467 GB); splice mover = the embed-gather launch of the step.
-NCU_TRAFFIC = {"cfg2_clip_l14_336_llama8b": {"gemm": 1.3256e9, "attention": 1.1849e9, "layernorm": 0.5464e9}}
+# cfg2 B=256 (profiles/r01h_ncu_full_summary.txt): GEMM = mean over one encoder layer's four launches
+# (fc2+stats 1.818, qkv(LN folded) 1.182, out-proj+stats 0.877, fc1(LN folded) 1.487 GB).
+NCU_TRAFFIC = {"cfg2_clip_l14_336_llama8b": {"gemm": 1.341e9, "attention": 1.1849e9, "layernorm": 0.5464e9}}
 
 
 def workload(wl):
@@ -236,6 +236,17 @@ def run_b200(args):
         status_h.copy_(embedder.status(), non_blocking=True)            # + the data-dependent error word
         return out
 
+    # ---- raw uint8 host images for `e2e_uint8`: the same call, resize/crop/normalise on the device
+    raw_h = torch.randint(0, 256, (images, cfg.image_size, cfg.image_size, 3), dtype=torch.uint8,
+                          generator=torch.Generator().manual_seed(300 + rank)).pin_memory()
+    pmi_raw = {"stacked": {"image": raw_h}, "batch_idx": {}, "token_range": {}}
+
+    def step_e2e_u8():
+        out = embedder(ids_h, pmi_raw, positions_from="device")        # H2D of ids + raw bytes, pre-processing inside
+        result_h.copy_(out.view(-1, H)[-1], non_blocking=True)
+        status_h.copy_(embedder.status(), non_blocking=True)
+        return out
+
     def barrier():
         if world > 1:
             dist.barrier()
@@ -270,6 +281,11 @@ def run_b200(args):
     for _ in range(2):
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
+    for _ in range(2):
+        step_e2e_u8()
+    ops.LAUNCHES = 0
+    ms_e2e_u8 = timed(step_e2e_u8, args.steps)
+    launches_u8 = ops.LAUNCHES // args.steps
     if sampler:
         sampler.mark_end()
     clocks = sampler.stop() if sampler else None
@@ -304,6 +320,11 @@ def run_b200(args):
         "clocks": clocks,
         "e2e": {"value": total_images * P / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": int(px.numel() * 4 + ids.numel() * 8), "d2h_bytes_per_step": int(H * 2 + 4)},
+        "e2e_uint8": {"value": total_images * P / (ms_e2e_u8 * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e_u8,
+                      "h2d_bytes_per_step": int(raw_h.numel() + ids.numel() * 8), "d2h_bytes_per_step": int(H * 2 + 4),
+                      "gpu_launches_per_step": launches_u8,
+                      "note": "same call fed RAW uint8 [H,W,3] host images: resize/crop/normalise run on the device "
+                              "(mm_preprocess_images, bit-exact vs the HF processor) instead of on the CPU"},
         "gpu_launches": launches_per_step * args.steps,
         "gpu_launches_per_step": launches_per_step,
         "roofline": {"kernel": "gemm_bf16_tn_kernel<false> (tcgen05 GEMM, %d launches/step)" % (n_gemm // max(1, args.steps)),
@@ -311,7 +332,7 @@ def run_b200(args):
                      "frac": gemm_tf / pk["tf_sust"],
                      "traffic": NCU_TRAFFIC.get(args.workload, {}).get("gemm") if images == w["images"] else None,
                      "traffic_src": "ncu --set full, mean bytes per launch over one encoder layer's 4 GEMMs "
-                                    "(profiles/r01c_ncu_full_summary.txt)",
+                                    "(profiles/r01h_ncu_full_summary.txt)",
                      "peak_kind": f"{pk['src']} sustained cuBLAS bf16 (kernel timed inside a long step)",
                      "frac_of_burst": gemm_tf / pk["tf_burst"]},
         "path_tensor": {"achieved": path_tf, "unit": "TFLOP/s", "frac_of_sustained": path_tf / pk["tf_sust"],

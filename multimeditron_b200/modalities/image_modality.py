@@ -130,6 +130,10 @@ class B200ImageModality(BaseModality):
     def _stack(self, inputs) -> torch.Tensor:
         dev = self.runner.w.device
         if torch.is_tensor(inputs):
+            if inputs.dtype == torch.uint8:                  # [B,H,W,3] raw images in one (pinned) tensor
+                if self._pre is None:
+                    self._pre = DevicePreprocessor.for_tower(self.tower)
+                return self._pre(inputs, dev, torch.bfloat16)
             return inputs.to(dev, non_blocking=True)
         inputs = list(inputs)
         if len(inputs) and inputs[0].dtype == torch.uint8:   # raw [H,W,3] images: pre-process on the device

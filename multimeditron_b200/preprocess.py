@@ -78,6 +78,7 @@ class DevicePreprocessor:
         self.std255 = (torch.tensor(std, dtype=torch.float32) * k).tolist()
         self._staging = None
         self._event = None
+        self._bplan = None
 
     @classmethod
     def for_tower(cls, tower) -> "DevicePreprocessor":
@@ -85,7 +86,29 @@ class DevicePreprocessor:
             return cls(tower.image_size, (0.5, 0.5, 0.5), (0.5, 0.5, 0.5), square=True)
         return cls(tower.image_size)
 
+    def _batched(self, images: torch.Tensor, device, out_dtype) -> torch.Tensor:
+        """One uint8 [B,H,W,3] tensor (same-size images, e.g. a pinned host batch): no packing copy — the tensor itself
+        is the source buffer, only the small descriptor table is staged."""
+        B, H, W, C = images.shape
+        if images.dtype != torch.uint8 or C != 3:
+            raise ValueError(f"raw images must be uint8 [B,H,W,3], got {images.dtype} {tuple(images.shape)}")
+        if B == 0:
+            return torch.empty(0, 3, self.size, self.size, dtype=out_dtype, device=device)
+        if (H * W * 3) % 4:
+            return self([images[i] for i in range(B)], device, out_dtype)   # keep every image 4-byte aligned
+        key = (B, H, W)
+        if self._bplan is None or self._bplan[0] != key:
+            plan = plan_batch([(H, W)] * B, self.size, self.square)
+            desc = torch.from_numpy(plan.desc).pin_memory()
+            self._bplan = (key, plan, desc, desc.to(device))              # descriptors of a fixed shape never change
+        _, plan, _, desc_dev = self._bplan
+        src = images.contiguous().to(device, non_blocking=True).view(-1)
+        return ops.preprocess_images(src, desc_dev, self.size, plan.kmax, plan.max_h, plan.max_w, plan.tmp_bytes,
+                                     self.mean255, self.std255, out_dtype)
+
     def __call__(self, images, device, out_dtype=torch.float32) -> torch.Tensor:
+        if torch.is_tensor(images) and images.dim() == 4:
+            return self._batched(images, device, out_dtype)
         images = [torch.from_numpy(np.ascontiguousarray(im)) if isinstance(im, np.ndarray) else im for im in images]
         for im in images:
             if im.dtype != torch.uint8 or im.dim() != 3 or im.shape[2] != 3:

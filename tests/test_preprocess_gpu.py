@@ -75,3 +75,17 @@ def test_modality_forward_on_raw_uint8_equals_forward_on_processed_pixels():
     y_px = m([torch.from_numpy(po.clip_preprocess(r, TOWERS["tiny"].image_size)) for r in raws])
     assert y_raw.shape == (3, TOWERS["tiny"].num_patches, 64)
     assert torch.equal(y_raw, y_px)
+
+
+def test_batched_uint8_tensor_path_equals_list_path():
+    """[B,H,W,3] uint8 tensor (pinned host batch, no packing copy) == list-of-images path, through the modality."""
+    cfg = AutoModality.config_from_dict({"model_type": "meditron_clip_b200", "hidden_size": 64, "clip_name": "tiny"})
+    m = AutoModality.from_config(cfg).load_reference_state_dict(synth.make_modality_state_dict(TOWERS["tiny"], 64, seed=3), DEV)
+    raw = torch.randint(0, 256, (5, 48, 64, 3), dtype=torch.uint8, generator=torch.Generator().manual_seed(2))
+    y_list = m([raw[i] for i in range(5)])
+    y_batch = m(raw.pin_memory())
+    assert torch.equal(y_list, y_batch)
+    p = pre.DevicePreprocessor(32)
+    a = p(raw, torch.device(DEV), torch.float32).cpu()
+    for i in range(5):
+        assert torch.equal(a[i], torch.from_numpy(po.clip_preprocess(raw[i].numpy(), 32)))
