@@ -34,7 +34,12 @@ WORKLOADS = {
     "cfg3_siglip_so400m_qwen7b": ("siglip_so400m_384", 3584, 64, 64, 152_064),
     # BASELINE configs[3]: interleaved rows, 4 images per 8192-token row (cfg2 encoder), 64 rows = 256 images
     "cfg4_interleaved_8k": ("clip_l14_336", 4096, 256, 0, 128_258, 4, 8192),
+    # BASELINE configs[4]: expert-routed image modality (cookbook moe/alignment/avg/shared): 5 CLIP-B/32 experts run
+    # on every image, gating-weighted average, shared projector into hidden 4096; RAW mixed-resolution uint8 images
+    # ({224,336,512,1024}^2) resized on the device; gating weights are synthetic (the ResNet-50 gate is §8(f) rank 3)
+    "cfg5_moe_5x_clip_b32_llama8b": ("clip_b32", 4096, 256, 64, 128_258),
 }
+MOE_EXPERTS = {"cfg5_moe_5x_clip_b32_llama8b": 5}
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` capture of this command at
 # cfg2 B=256 (profiles/r01h_ncu_full_summary.txt): GEMM = mean over one encoder layer's four launches
@@ -211,18 +216,37 @@ def run_b200(args):
     P = cfg.num_patches
 
     # weights: replicated on every GPU (same seed), random init of the named architecture
-    sd = synth.make_modality_state_dict(cfg, H, seed=0, dtype=torch.bfloat16)
-    mcfg = AutoModality.config_from_dict({"model_type": "meditron_clip_b200", "hidden_size": H, "clip_name": tower})
-    modality = AutoModality.from_config(mcfg).load_reference_state_dict(sd, dev)
+    E = MOE_EXPERTS.get(args.workload, 0)
+    if E:
+        names = [f"expert{i}" for i in range(E)]
+        order = torch.randperm(E, generator=torch.Generator().manual_seed(5)).tolist()   # shuffled gating class order
+        mcfg = AutoModality.config_from_dict({
+            "model_type": "moe_meditron_clip_b200", "hidden_size": H, "expert_clip_names": names,
+            "expert_towers": {n: tower for n in names}, "image_processor": tower, "fusion_method": "weighted_average",
+            "top_k_experts": 1, "gating_class_names": [names[i] for i in order]})
+        sd = synth.make_moe_state_dict([cfg] * E, H, False, seed=0, dtype=torch.bfloat16)
+        gate_w = torch.softmax(torch.randn(images, E, generator=torch.Generator().manual_seed(7 + rank)), -1).to(dev)
+        modality = AutoModality.from_config(mcfg).load_reference_state_dict(sd, dev, gating=lambda _px: gate_w)
+        # raw mixed-resolution images, packed once (what the collator would hand over), resized on the device
+        from multimeditron_b200.preprocess import DevicePreprocessor
+        g = torch.Generator().manual_seed(400 + rank)
+        sizes = [(224, 336, 512, 1024)[int(i)] for i in torch.randint(0, 4, (images,), generator=g)]
+        packed = DevicePreprocessor.for_tower(cfg).pack(
+            [torch.randint(0, 256, (n, n, 3), dtype=torch.uint8, generator=g) for n in sizes])
+        px = packed.buf            # byte count of the step's image input
+    else:
+        sd = synth.make_modality_state_dict(cfg, H, seed=0, dtype=torch.bfloat16)
+        mcfg = AutoModality.config_from_dict({"model_type": "meditron_clip_b200", "hidden_size": H, "clip_name": tower})
+        modality = AutoModality.from_config(mcfg).load_reference_state_dict(sd, dev)
     del sd
     table = (torch.randn(V, H, generator=torch.Generator().manual_seed(1)) * 0.02).bfloat16().to(dev)
     embedder = B200MultiModalEmbedder(table, [modality], att)
 
     # ---- device-resident inputs for `value`
-    ids_d, px_d = ids.to(dev), px.to(dev)
+    ids_d, px_d = ids.to(dev), (packed.to(dev) if E else px.to(dev))
     pmi_dev = {"stacked": {"image": px_d}, "batch_idx": {}, "token_range": {}}
     # ---- host (pinned) inputs for `e2e`
-    ids_h, px_h = ids.pin_memory(), px.pin_memory()
+    ids_h, px_h = ids.pin_memory(), (packed if E else px.pin_memory())
     pmi_host = {"stacked": {"image": px_h}, "batch_idx": {}, "token_range": {}}
     result_h = torch.empty(H, dtype=torch.bfloat16).pin_memory()
     status_h = torch.empty(1, dtype=torch.int32).pin_memory()
@@ -305,6 +329,10 @@ def run_b200(args):
     total_images = images * world
     pk = peaks()
     flops_img = cfg.flops_per_image(H)
+    if E:   # every expert's tower on every image + ONE shared projector
+        D = cfg.hidden_size
+        proj_fl = 2.0 * P * (D * D + D * H + H * H)
+        flops_img = E * (flops_img - proj_fl) + proj_fl
     n_gemm, ms_gemm, fl_gemm = prof.get("mm_gemm_bias_act", (0, 0.0, 0.0))
     gemm_tf = fl_gemm / (ms_gemm * 1e-3) / 1e12 if ms_gemm else 0.0
     path_tf = flops_img * images / (ms * 1e-3) / 1e12
@@ -315,11 +343,12 @@ def run_b200(args):
         "config": {"workload": args.workload, "tower": tower, "llm_hidden": H, "images_per_gpu": images,
                    "global_images": total_images, "rows_per_gpu": ids.shape[0], "seq_len": S, "tokens_per_image": P, "parallelism": f"sample-shard x{world}",
                    "l2": "inputs larger than L2 (pixels %.0f MB, inputs_embeds %.0f MB per step)" % (
-                       px.numel() * 4 / 1e6, ids.shape[0] * S * H * 2 / 1e6),
+                       px.numel() * px.element_size() / 1e6, ids.shape[0] * S * H * 2 / 1e6),
                    "positions": "device prefix sum", "splice": "fused into the last projector GEMM epilogue"},
         "clocks": clocks,
         "e2e": {"value": total_images * P / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
-                "h2d_bytes_per_step": int(px.numel() * 4 + ids.numel() * 8), "d2h_bytes_per_step": int(H * 2 + 4)},
+                "h2d_bytes_per_step": int(px.numel() * px.element_size() + ids.numel() * 8),
+                "d2h_bytes_per_step": int(H * 2 + 4)},
         "e2e_uint8": {"value": total_images * P / (ms_e2e_u8 * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e_u8,
                       "h2d_bytes_per_step": int(raw_h.numel() + ids.numel() * 8), "d2h_bytes_per_step": int(H * 2 + 4),
                       "gpu_launches_per_step": launches_u8,
@@ -344,7 +373,11 @@ def run_b200(args):
                             "ms": ms_sp, "traffic": None},
         "op_ms_per_step": {k: v[1] / args.steps for k, v in sorted(prof.items())},
     }
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if E:
+        line["config"]["experts"] = E
+        line["config"]["inputs"] = "raw uint8 images, sizes drawn from {224,336,512,1024}^2, resized on the device"
+        line["config"]["gating"] = "synthetic softmax weights (ResNet-50 gate not on the path, SURVEY §8(f) rank 3)"
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and not E:
         threads = os.cpu_count() or 1
         toks, _, desc = cpu_reference_leg(args.workload, args.cpu_sample, 1, 1, threads)
         line["cpu_baseline"] = {"value": toks, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc}

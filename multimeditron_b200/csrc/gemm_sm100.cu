@@ -51,7 +51,7 @@ struct GemmCfg {
 };
 static_assert(sizeof(GemmSmemTail) <= 256, "tail too large");
 static_assert(GemmCfg<false>::kSmemBytes <= 232448, "smem budget");
-static_assert(GemmCfg<true>::kSmemBytes + kKTableMax * 4 <= 232448, "smem budget (gather)");
+static_assert(GemmCfg<true>::kSmemBytes + kKTableMax * 4 + kKTableMax / 8 <= 232448, "smem budget (gather)");
 
 struct GemmParams {
   __nv_bfloat16* C;
@@ -155,6 +155,7 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
   uint8_t* sEpi = sB + kStages * kBStageBytes;
   GemmSmemTail* tail = reinterpret_cast<GemmSmemTail*>(sEpi + Cfg::kEpiBytes);
   __shared__ int s_koff[kGatherA ? kKTableMax : 1];
+  __shared__ uint8_t s_kcontig[kGatherA ? kKTableMax / 8 : 1];  // 1: the 8 pixels of this k-group are consecutive in memory
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -191,6 +192,11 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
         off = c * p.img * p.img + ky * p.img + kx;
       }
       s_koff[k] = off;
+    }
+    for (int g = threadIdx.x; g < num_kb * (BK / 8); g += blockDim.x) {
+      const int k0 = g * 8;   // same channel, same patch row, 8 consecutive kx, all real
+      const int c0 = k0 / pp, r0 = k0 - c0 * pp;
+      s_kcontig[g] = (k0 + 7 < p.k_real && (k0 + 7) / pp == c0 && (r0 % p.patch) + 7 < p.patch) ? 1 : 0;
     }
   }
   tc_fence_before();
@@ -455,17 +461,47 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
         const uint32_t dst = smem_u32(sA + stage * kAStageBytes) + row * 128;
 #pragma unroll 2
         for (int j = 0; j < 8; ++j) {
-          float f[8];
+          uint32_t w4[4] = {0u, 0u, 0u, 0u};   // 8 bf16 of this row's k-group
+          const int g = kb * (BK / 8) + j;
+          const int64_t a0 = base + s_koff[g * 8];
+          if (base >= 0 && s_kcontig[g] && (a0 & 1) == 0) {
+            // 8 consecutive pixels: vector loads as wide as the alignment allows (patch 32: always 16 bytes)
+            if (p.pixel_is_f32) {
+              if ((a0 & 3) == 0) {
+                const float4 u = __ldg(reinterpret_cast<const float4*>(px32 + a0));
+                const float4 v = __ldg(reinterpret_cast<const float4*>(px32 + a0) + 1);
+                w4[0] = pack_bf16x2(u.x, u.y), w4[1] = pack_bf16x2(u.z, u.w);
+                w4[2] = pack_bf16x2(v.x, v.y), w4[3] = pack_bf16x2(v.z, v.w);
+              } else {
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int off = s_koff[kb * BK + j * 8 + e];
-            float v = 0.f;
-            if (base >= 0 && off >= 0) v = p.pixel_is_f32 ? __ldg(px32 + base + off) : __bfloat162float(px16[base + off]);
-            f[e] = v;
+                for (int e = 0; e < 4; ++e) {
+                  const float2 u = __ldg(reinterpret_cast<const float2*>(px32 + a0) + e);
+                  w4[e] = pack_bf16x2(u.x, u.y);
+                }
+              }
+            } else {
+              if ((a0 & 7) == 0) {
+                const uint4 u = __ldg(reinterpret_cast<const uint4*>(px16 + a0));
+                w4[0] = u.x, w4[1] = u.y, w4[2] = u.z, w4[3] = u.w;
+              } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) w4[e] = __ldg(reinterpret_cast<const uint32_t*>(px16 + a0) + e);
+              }
+            }
+          } else {
+            float f[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const int off = s_koff[g * 8 + e];
+              float v = 0.f;
+              if (base >= 0 && off >= 0) v = p.pixel_is_f32 ? __ldg(px32 + base + off) : __bfloat162float(px16[base + off]);
+              f[e] = v;
+            }
+            w4[0] = pack_bf16x2(f[0], f[1]), w4[1] = pack_bf16x2(f[2], f[3]);
+            w4[2] = pack_bf16x2(f[4], f[5]), w4[3] = pack_bf16x2(f[6], f[7]);
           }
-          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + ((j ^ (row & 7)) << 4)),
-                       "r"(pack_bf16x2(f[0], f[1])), "r"(pack_bf16x2(f[2], f[3])), "r"(pack_bf16x2(f[4], f[5])),
-                       "r"(pack_bf16x2(f[6], f[7]))
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + ((j ^ (row & 7)) << 4)), "r"(w4[0]),
+                       "r"(w4[1]), "r"(w4[2]), "r"(w4[3])
                        : "memory");
         }
         fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor-core (async) proxy
@@ -695,7 +731,8 @@ extern "C" int mm_patch_embed(const void* pixels, int pixel_dtype, int64_t B, in
   const int64_t Kpad = (Kreal + BK - 1) / BK * BK;
   if (Kpad > kKTableMax || ldw < Kpad || ldw % 8) return MM_ERR_BAD_ARG;  // weight must be zero-padded to Kpad
   if (B * P > INT32_MAX / 2 || B * 3 * img * img > (int64_t)INT32_MAX * 4) return MM_ERR_BAD_ARG;
-  if (!aligned16(weight) || !aligned16(conv_bias) || !aligned16(pos_emb) || !aligned16(out)) return MM_ERR_BAD_ARG;
+  if (!aligned16(pixels) || !aligned16(weight) || !aligned16(conv_bias) || !aligned16(pos_emb) || !aligned16(out))
+    return MM_ERR_BAD_ARG;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int cls_rows = cls ? 1 : 0;
   const int64_t T = P + cls_rows;

@@ -13,7 +13,7 @@ from typing import Any, Dict, List, Optional
 import torch
 
 from ..configs import TOWERS, TowerConfig
-from ..preprocess import DevicePreprocessor
+from ..preprocess import DevicePreprocessor, PackedImages
 from ..vit import ProjectorWeights, TowerRunner, TowerWeights
 from .base import AutoModality, BaseModality, BaseModalityConfig, BaseModalityProcessor
 from .constants import MODALITY_VALUE_KEY, NUM_EMBEDDINGS_KEY, POSITION_IDS_KEY
@@ -129,8 +129,12 @@ class B200ImageModality(BaseModality):
     # -- the plugin call ----------------------------------------------------------------------------------------
     def _stack(self, inputs) -> torch.Tensor:
         dev = self.runner.w.device
+        if isinstance(inputs, PackedImages) or (torch.is_tensor(inputs) and inputs.dtype == torch.uint8):
+            if self._pre is None:                            # packed ragged batch / [B,H,W,3] raw images in one tensor
+                self._pre = DevicePreprocessor.for_tower(self.tower)
+            return self._pre(inputs, dev, torch.bfloat16)
         if torch.is_tensor(inputs):
-            if inputs.dtype == torch.uint8:                  # [B,H,W,3] raw images in one (pinned) tensor
+            if inputs.dtype == torch.uint8:
                 if self._pre is None:
                     self._pre = DevicePreprocessor.for_tower(self.tower)
                 return self._pre(inputs, dev, torch.bfloat16)

@@ -22,6 +22,7 @@ import torch
 
 from .. import ops
 from ..configs import TowerConfig
+from ..preprocess import DevicePreprocessor, PackedImages
 from ..vit import ProjectorWeights, TowerRunner, TowerWeights
 from .base import AutoModality, BaseModality, BaseModalityConfig, BaseModalityProcessor
 from .constants import MODALITY_VALUE_KEY, NUM_EMBEDDINGS_KEY
@@ -133,6 +134,7 @@ class _B200MOEBase(BaseModality):
             perm = list(range(len(self.towers)))
         self._perm_list = perm
         self._gating = gating
+        self._pre: Optional[DevicePreprocessor] = None
         self._runners: List[TowerRunner] = []
         self._projs: List[ProjectorWeights] = []
         self._maps: Dict[Any, torch.Tensor] = {}
@@ -176,6 +178,13 @@ class _B200MOEBase(BaseModality):
     def _stack(self, inputs) -> torch.Tensor:
         if not self._runners:
             raise RuntimeError("no weights loaded (call load_reference_state_dict)")
+        raw_list = isinstance(inputs, (list, tuple)) and len(inputs) and inputs[0].dtype == torch.uint8
+        if isinstance(inputs, PackedImages) or raw_list or (torch.is_tensor(inputs) and inputs.dtype == torch.uint8):
+            # raw uint8 images (mixed resolutions): resize / crop / normalise on the device, bit-exact with the
+            # experts' shared HF image processor (image_modality_moe.py:96-99 of the reference)
+            if self._pre is None:
+                self._pre = DevicePreprocessor.for_tower(self.towers[0])
+            return self._pre(inputs, self._device, torch.bfloat16)
         if torch.is_tensor(inputs):
             return inputs.to(self._device, non_blocking=True)
         inputs = list(inputs)

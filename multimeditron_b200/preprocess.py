@@ -66,6 +66,24 @@ def plan_batch(shapes, size: int, square: bool) -> Plan:
     return Plan(desc, src, tmp, kmax, mh, mw)
 
 
+class PackedImages:
+    """A ragged batch of raw images packed once: `buf` (uint8, pinned host or device) = images at their descriptor
+    offsets followed by the int64 descriptor table; what a data loader would hand over instead of fp32 pixel tensors."""
+
+    def __init__(self, buf: torch.Tensor, plan: Plan, desc_off: int):
+        self.buf, self.plan, self.desc_off = buf, plan, desc_off
+
+    def __len__(self) -> int:
+        return self.plan.desc.shape[0]
+
+    def to(self, device) -> "PackedImages":
+        return PackedImages(self.buf.to(device, non_blocking=True), self.plan, self.desc_off)
+
+    @property
+    def nbytes(self) -> int:
+        return self.buf.numel()
+
+
 class DevicePreprocessor:
     """`pre(images) -> Tensor[B,3,S,S]` on the device; images are uint8 [H,W,3] tensors / arrays (CPU or CUDA)."""
 
@@ -106,7 +124,32 @@ class DevicePreprocessor:
         return ops.preprocess_images(src, desc_dev, self.size, plan.kmax, plan.max_h, plan.max_w, plan.tmp_bytes,
                                      self.mean255, self.std255, out_dtype)
 
+    def pack(self, images, pin: bool = True) -> PackedImages:
+        """Host-side packing of a ragged list of uint8 [H,W,3] images (done once per batch, e.g. by the collator)."""
+        images = [torch.from_numpy(np.ascontiguousarray(im)) if isinstance(im, np.ndarray) else im for im in images]
+        for im in images:
+            if im.dtype != torch.uint8 or im.dim() != 3 or im.shape[2] != 3:
+                raise ValueError(f"raw images must be uint8 [H,W,3], got {im.dtype} {tuple(im.shape)}")
+        plan = plan_batch([(im.shape[0], im.shape[1]) for im in images], self.size, self.square)
+        desc_off = (plan.src_bytes + 7) & ~7
+        buf = torch.empty(desc_off + plan.desc.nbytes, dtype=torch.uint8, pin_memory=pin)
+        for im, d in zip(images, plan.desc):
+            buf[int(d[0]):int(d[0]) + im.numel()].copy_(im.contiguous().view(-1))
+        buf[desc_off:].copy_(torch.from_numpy(plan.desc.view(np.uint8).reshape(-1)))
+        return PackedImages(buf, plan, desc_off)
+
+    def _packed(self, packed: PackedImages, device, out_dtype) -> torch.Tensor:
+        if len(packed) == 0:
+            return torch.empty(0, 3, self.size, self.size, dtype=out_dtype, device=device)
+        plan = packed.plan
+        buf = packed.buf if packed.buf.is_cuda else packed.buf.to(device, non_blocking=True)   # ONE H2D per batch
+        desc = buf[packed.desc_off:].view(torch.int64).view(-1, DESC_FIELDS)
+        return ops.preprocess_images(buf, desc, self.size, plan.kmax, plan.max_h, plan.max_w, plan.tmp_bytes,
+                                     self.mean255, self.std255, out_dtype)
+
     def __call__(self, images, device, out_dtype=torch.float32) -> torch.Tensor:
+        if isinstance(images, PackedImages):
+            return self._packed(images, device, out_dtype)
         if torch.is_tensor(images) and images.dim() == 4:
             return self._batched(images, device, out_dtype)
         images = [torch.from_numpy(np.ascontiguousarray(im)) if isinstance(im, np.ndarray) else im for im in images]
