@@ -1,0 +1,55 @@
+"""Double-buffered host->device upload on a side stream.
+
+The reference uploads the step's pixel tensor synchronously from pageable memory (image_modality.py:131-132).  Here a
+pinned host tensor is copied on a dedicated copy stream into one of `depth` persistent device buffers; the compute
+stream only waits for that copy's event.  Because the host enqueues step i+1 while the GPU still runs step i, the copy
+of step i+1 overlaps step i's kernels and disappears from the critical path.  A buffer is written again only after the
+step that read it has released it (event recorded on the compute stream)."""
+from __future__ import annotations
+
+import torch
+
+
+class H2DUploader:
+    def __init__(self, device, depth: int = 2):
+        self.device = torch.device(device)
+        self.stream = torch.cuda.Stream(device=self.device)
+        self.slots = [dict(buf=None, free=None) for _ in range(depth)]
+        self.i = 0
+        self.in_use = []
+        self.last_ready = None
+
+    def upload(self, host: torch.Tensor) -> torch.Tensor:
+        """-> device copy of `host`, valid on the CURRENT stream.  Non-pinned input degrades to a plain async copy."""
+        if host.is_cuda:
+            return host
+        if not host.is_pinned():
+            return host.to(self.device, non_blocking=True)
+        slot = self.slots[self.i]
+        self.i = (self.i + 1) % len(self.slots)
+        cur = torch.cuda.current_stream(self.device)
+        buf = slot["buf"]
+        if buf is None or buf.shape != host.shape or buf.dtype != host.dtype:
+            buf = slot["buf"] = torch.empty(host.shape, dtype=host.dtype, device=self.device)
+            slot["free"] = None
+            self.stream.wait_stream(cur)      # the allocator may hand out memory whose last user is still queued on `cur`
+        if slot["free"] is not None:
+            self.stream.wait_event(slot["free"])
+        with torch.cuda.stream(self.stream):
+            buf.copy_(host, non_blocking=True)
+            ready = torch.cuda.Event()
+            ready.record(self.stream)
+        cur.wait_event(ready)
+        self.last_ready = ready
+        self.in_use.append(slot)
+        return buf
+
+    def release(self):
+        """Call once the kernels that read the uploaded buffers have been enqueued on the current stream."""
+        if not self.in_use:
+            return
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        for slot in self.in_use:
+            slot["free"] = ev
+        self.in_use = []

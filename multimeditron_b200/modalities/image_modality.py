@@ -13,6 +13,7 @@ from typing import Any, Dict, List, Optional
 import torch
 
 from ..configs import TOWERS, TowerConfig
+from ..h2d import H2DUploader
 from ..preprocess import DevicePreprocessor, PackedImages
 from ..vit import ProjectorWeights, TowerRunner, TowerWeights
 from .base import AutoModality, BaseModality, BaseModalityConfig, BaseModalityProcessor
@@ -99,6 +100,7 @@ class B200ImageModality(BaseModality):
         self._staging: Optional[torch.Tensor] = None
         self._staging_event = None
         self._pre: Optional[DevicePreprocessor] = None
+        self._up: Optional[H2DUploader] = None
         self._frozen = True
         if state_dict is not None:
             self.load_reference_state_dict(state_dict, device or torch.device("cuda", torch.cuda.current_device()))
@@ -127,23 +129,28 @@ class B200ImageModality(BaseModality):
         return self._runner
 
     # -- the plugin call ----------------------------------------------------------------------------------------
+    def _preprocessor(self) -> DevicePreprocessor:
+        if self._pre is None:
+            self._pre = DevicePreprocessor.for_tower(self.tower)
+            self._pre.uploader = self._uploader()
+        return self._pre
+
+    def _uploader(self) -> H2DUploader:
+        if self._up is None:
+            self._up = H2DUploader(self.runner.w.device)
+        return self._up
+
     def _stack(self, inputs) -> torch.Tensor:
+        """-> [B,3,S,S] pixels on the device.  Host inputs travel on the copy stream (h2d.H2DUploader); raw uint8
+        images (list of [H,W,3], one [B,H,W,3] tensor, or PackedImages) are pre-processed on the device."""
         dev = self.runner.w.device
         if isinstance(inputs, PackedImages) or (torch.is_tensor(inputs) and inputs.dtype == torch.uint8):
-            if self._pre is None:                            # packed ragged batch / [B,H,W,3] raw images in one tensor
-                self._pre = DevicePreprocessor.for_tower(self.tower)
-            return self._pre(inputs, dev, torch.bfloat16)
+            return self._preprocessor()(inputs, dev, torch.bfloat16)
         if torch.is_tensor(inputs):
-            if inputs.dtype == torch.uint8:
-                if self._pre is None:
-                    self._pre = DevicePreprocessor.for_tower(self.tower)
-                return self._pre(inputs, dev, torch.bfloat16)
-            return inputs.to(dev, non_blocking=True)
+            return self._uploader().upload(inputs)
         inputs = list(inputs)
         if len(inputs) and inputs[0].dtype == torch.uint8:   # raw [H,W,3] images: pre-process on the device
-            if self._pre is None:
-                self._pre = DevicePreprocessor.for_tower(self.tower)
-            return self._pre(inputs, dev, torch.bfloat16)
+            return self._preprocessor()(inputs, dev, torch.bfloat16)
         if len(inputs) and inputs[0].is_cuda:
             return torch.stack(inputs, dim=0)
         # one cached pinned staging buffer + one async H2D instead of the reference's pageable, synchronous
@@ -157,20 +164,27 @@ class B200ImageModality(BaseModality):
         if self._staging_event is not None:
             self._staging_event.synchronize()  # the previous H2D out of this buffer must have finished
         torch.stack(inputs, dim=0, out=buf)
-        out = buf.to(dev, non_blocking=True)
-        self._staging_event = torch.cuda.Event()
-        self._staging_event.record()
+        out = self._uploader().upload(buf)
+        self._staging_event = self._uploader().last_ready
         return out
+
+    def _release(self):
+        if self._up is not None:
+            self._up.release()
 
     @torch.no_grad()
     def forward(self, inputs: List[torch.Tensor]) -> torch.Tensor:
-        return self.runner.forward(self._stack(inputs))
+        y = self.runner.forward(self._stack(inputs))
+        self._release()
+        return y
 
     @torch.no_grad()
     def forward_into(self, inputs, embedded_tokens: torch.Tensor, dest_rows: torch.Tensor) -> torch.Tensor:
         """forward + splice in one go: projected row k lands in embedded_tokens.view(-1,H)[dest_rows[k]]."""
         r = self.runner
-        return r.project(r.features(self._stack(inputs)), out=embedded_tokens, out_row_map=dest_rows)
+        y = r.project(r.features(self._stack(inputs)), out=embedded_tokens, out_row_map=dest_rows)
+        self._release()
+        return y
 
     # -- training-mode switches (interface parity; backward is not part of this round) ------------------------------
     def freeze_modality_embedder(self):

@@ -22,6 +22,7 @@ import torch
 
 from .. import ops
 from ..configs import TowerConfig
+from ..h2d import H2DUploader
 from ..preprocess import DevicePreprocessor, PackedImages
 from ..vit import ProjectorWeights, TowerRunner, TowerWeights
 from .base import AutoModality, BaseModality, BaseModalityConfig, BaseModalityProcessor
@@ -184,6 +185,7 @@ class _B200MOEBase(BaseModality):
             # experts' shared HF image processor (image_modality_moe.py:96-99 of the reference)
             if self._pre is None:
                 self._pre = DevicePreprocessor.for_tower(self.towers[0])
+                self._pre.uploader = H2DUploader(self._device)     # host bytes travel on a copy stream
             return self._pre(inputs, self._device, torch.bfloat16)
         if torch.is_tensor(inputs):
             return inputs.to(self._device, non_blocking=True)
@@ -226,6 +228,7 @@ class _B200MOEBase(BaseModality):
         n_out = P if self.fusion_method == "weighted_average" else E * P
         out = torch.empty(B, n_out, H, dtype=torch.bfloat16, device=self._device)
         self._run(px, out.view(-1, H), None)
+        self._release()
         return out
 
     @torch.no_grad()
@@ -233,7 +236,12 @@ class _B200MOEBase(BaseModality):
         """forward + splice: output row k lands in embedded_tokens.view(-1,H)[dest_rows[k]] (model.py:441-444)."""
         px = self._stack(inputs)
         self._run(px, embedded_tokens.view(-1, embedded_tokens.shape[-1]), dest_rows)
+        self._release()
         return embedded_tokens
+
+    def _release(self):
+        if self._pre is not None and self._pre.uploader is not None:
+            self._pre.uploader.release()
 
     def _run(self, px: torch.Tensor, out2d: torch.Tensor, dest_rows: Optional[torch.Tensor]):
         raise NotImplementedError

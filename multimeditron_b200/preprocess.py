@@ -97,6 +97,12 @@ class DevicePreprocessor:
         self._staging = None
         self._event = None
         self._bplan = None
+        self.uploader = None     # optional h2d.H2DUploader: host buffers then travel on its copy stream
+
+    def _h2d(self, host: torch.Tensor, device) -> torch.Tensor:
+        if self.uploader is not None:
+            return self.uploader.upload(host)
+        return host.to(device, non_blocking=True)
 
     @classmethod
     def for_tower(cls, tower) -> "DevicePreprocessor":
@@ -120,7 +126,7 @@ class DevicePreprocessor:
             desc = torch.from_numpy(plan.desc).pin_memory()
             self._bplan = (key, plan, desc, desc.to(device))              # descriptors of a fixed shape never change
         _, plan, _, desc_dev = self._bplan
-        src = images.contiguous().to(device, non_blocking=True).view(-1)
+        src = self._h2d(images.contiguous(), device).view(-1)
         return ops.preprocess_images(src, desc_dev, self.size, plan.kmax, plan.max_h, plan.max_w, plan.tmp_bytes,
                                      self.mean255, self.std255, out_dtype)
 
@@ -142,7 +148,7 @@ class DevicePreprocessor:
         if len(packed) == 0:
             return torch.empty(0, 3, self.size, self.size, dtype=out_dtype, device=device)
         plan = packed.plan
-        buf = packed.buf if packed.buf.is_cuda else packed.buf.to(device, non_blocking=True)   # ONE H2D per batch
+        buf = packed.buf if packed.buf.is_cuda else self._h2d(packed.buf, device)   # ONE H2D per batch
         desc = buf[packed.desc_off:].view(torch.int64).view(-1, DESC_FIELDS)
         return ops.preprocess_images(buf, desc, self.size, plan.kmax, plan.max_h, plan.max_w, plan.tmp_bytes,
                                      self.mean255, self.std255, out_dtype)
