@@ -372,6 +372,7 @@ def run_b200(args):
                             "frac": splice_bytes / (ms_sp * 1e-3) / 1e9 / pk["hbm"], "bytes": splice_bytes,
                             "ms": ms_sp, "traffic": None},
         "op_ms_per_step": {k: v[1] / args.steps for k, v in sorted(prof.items())},
+        "roofline_attention": attention_roofline(cfg, images * (E or 1), prof, args.steps, clocks),
     }
     if E:
         line["config"]["experts"] = E
@@ -385,6 +386,23 @@ def run_b200(args):
         emit(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+def attention_roofline(cfg, images, prof, steps, clocks):
+    """The attention kernel is bound by the MUFU pipe (one ex2 per score; 16 per clock and SM), not by the tensor pipe:
+    report algorithmic exponentials/s against 148 SMs x 16/clk x the SM clock sampled under load."""
+    n, ms, _ = prof.get("mm_attention_fwd", (0, 0.0, 0.0))
+    if not ms:
+        return None
+    T = cfg.num_tokens
+    exps = float(images) * cfg.num_attention_heads * cfg.num_hidden_layers * T * T * steps
+    mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    peak = 148 * 16 * mhz * 1e6
+    ach = exps / (ms * 1e-3)
+    return {"kernel": "attention_fwd_kernel", "bound": "mufu", "achieved": ach / 1e12, "peak": peak / 1e12,
+            "unit": "Texp/s", "frac": ach / peak, "tflops": 4.0 * exps * cfg.head_dim / (ms * 1e-3) / 1e12,
+            "note": "algorithmic T*T exponentials per (image, head, layer); padding to 128-row/column tiles is not credited; "
+                    "peak = 148 SMs x 16 ex2/clk x median SM clock under load"}
 
 
 def main():

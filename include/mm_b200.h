@@ -205,6 +205,22 @@ int mm_attention_fwd(const void* qkv, void* out, int64_t B, int64_t T, int64_t h
 int mm_weighted_expert_sum(const void* x, const float* w, const int32_t* perm, void* out,
                            int64_t E, int64_t B, int64_t P, int64_t D, void* stream);
 
+/*
+ * mm_position_ids — the collator's position ids on the device (bit-exact integer work).
+ * Replaces src/multimeditron/model/data_loader.py:155-188:
+ *   use_2d == 0:  out [batch, seq] int64 = cumsum(attention_mask) - 1, 0 where the mask is 0            (:156-157)
+ *   use_2d != 0:  out [batch, seq, 2] int64: both components start as the 1-D ids; every image (a run of
+ *                 tokens_per_image = grid*grid attachment tokens, found from input_ids) gets (row, col) grid ids
+ *                 offset by the id at its first token, and everything behind it — padding included — is shifted by
+ *                 (largest id of the image's last token) - (1-D id of its last token, or 0 when the image opens the
+ *                 row: the reference's `token_range[0] > 0` clause, :178)                                 (:159-186)
+ *   attention_mask: int64 (HF) or uint8/bool (mask_is_u8).  At most 256 images per row; more, or an image block
+ *   that runs past the end of the row, sets MM_STATUS_COUNT_MISMATCH in `status` (may be NULL).
+ */
+int mm_position_ids(const int64_t* input_ids, const void* attention_mask, int mask_is_u8, int64_t batch,
+                    int64_t seq, int64_t attachment_id, int64_t tokens_per_image, int64_t grid, int use_2d,
+                    int64_t* out, int32_t* status, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Image pre-processing on the device — bit-exact byte/integer work, HBM-bound
  * ------------------------------------------------------------------------------------------ */

@@ -469,3 +469,147 @@ extern "C" int mm_embed_gather(void* out, int64_t n_pos, int64_t hidden, int dty
   a.hidden = hidden;
   return dispatch_move<3>(a, dtype, dtype, reinterpret_cast<cudaStream_t>(stream));
 }
+
+// ---------------------------------------------------------------------------------------------
+// position ids: the collator's `cumsum(mask) - 1` and its 2-D image variant
+// (src/multimeditron/model/data_loader.py:155-188) built on the device from input_ids + attention_mask.
+// One CTA per row: two block scans (mask count, image starts), a short serial pass over the row's images
+// (each image shifts everything behind it), one write pass.  Integer work, bit-exact.
+// ---------------------------------------------------------------------------------------------
+namespace mm {
+
+constexpr int kPosThreads = 512;
+constexpr int kPosMaxImages = 256;  // images per row
+
+__device__ __forceinline__ int block_exclusive_scan(int v, int* warp_sums, int& total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  __syncthreads();  // warp_sums may still be read from a previous scan
+  if (lane == 31) warp_sums[warp] = inc;
+  __syncthreads();
+  int base = 0, tot = 0;
+  for (int w = 0; w < kPosThreads / 32; ++w) {
+    const int s = warp_sums[w];
+    if (w < warp) base += s;
+    tot += s;
+  }
+  total = tot;
+  return base + inc - v;
+}
+
+template <typename MaskT>
+__global__ void __launch_bounds__(kPosThreads) position_ids_kernel(const int64_t* __restrict__ ids,
+                                                                   const MaskT* __restrict__ mask, int64_t* __restrict__ out,
+                                                                   int S, int64_t att, int P, int g, int use_2d,
+                                                                   int32_t* status) {
+  __shared__ int warp_sums[kPosThreads / 32];
+  __shared__ int s_start[kPosMaxImages];
+  __shared__ long long s_base[kPosMaxImages], s_shift[kPosMaxImages];
+  __shared__ int s_nimg;
+  const int b = blockIdx.x;
+  const int64_t* rid = ids + (int64_t)b * S;
+  const MaskT* rm = mask + (int64_t)b * S;
+  const int chunk = (S + kPosThreads - 1) / kPosThreads;
+  const int c0 = min(threadIdx.x * chunk, S), c1 = min(c0 + chunk, S);
+  int n_mask = 0, n_start = 0;
+  for (int t = c0; t < c1; ++t) {
+    n_mask += rm[t] != 0;
+    if (use_2d) n_start += (rid[t] == att) && (t == 0 || rid[t - 1] != att);
+  }
+  int tot_mask, tot_start = 0;
+  const int pre_mask = block_exclusive_scan(n_mask, warp_sums, tot_mask);
+  if (!use_2d) {
+    int run = pre_mask;
+    for (int t = c0; t < c1; ++t) {
+      const bool m = rm[t] != 0;
+      run += m;
+      out[(int64_t)b * S + t] = m ? run - 1 : 0;
+    }
+    return;
+  }
+  const int pre_start = block_exclusive_scan(n_start, warp_sums, tot_start);
+  int64_t* ro = out + (int64_t)b * S * 2;
+  {  // pass 1: 1-D ids (kept in component 0 for the serial pass) and the ordered list of image starts
+    int run = pre_mask, k = pre_start;
+    for (int t = c0; t < c1; ++t) {
+      const bool m = rm[t] != 0;
+      run += m;
+      ro[2 * (int64_t)t] = m ? run - 1 : 0;
+      if ((rid[t] == att) && (t == 0 || rid[t - 1] != att)) {
+        if (k < kPosMaxImages) s_start[k] = t;
+        ++k;
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int n = tot_start;
+    if (n > kPosMaxImages) {
+      n = kPosMaxImages;
+      if (status) atomicOr(status, MM_STATUS_COUNT_MISMATCH);
+    }
+    long long shift = 0;
+    for (int k = 0; k < n; ++k) {
+      const int t0 = s_start[k];
+      int t1 = t0 + P;
+      if (t1 > S) {  // an image block that does not fit the row: data error, reported like a count mismatch
+        t1 = S;
+        if (status) atomicOr(status, MM_STATUS_COUNT_MISMATCH);
+      }
+      const long long base = ro[2 * (int64_t)t0] + shift;                            // position at the first token (:179)
+      const long long old_last = t0 > 0 ? ro[2 * (int64_t)(t1 - 1)] + shift : 0;      // :178 (0 when the row starts with it)
+      const long long next_last = base + (g - 1);                                     // max of the last grid id (:180)
+      shift += next_last - old_last;                                                  // :186
+      s_base[k] = base;
+      s_shift[k] = shift;
+    }
+    s_nimg = n;
+  }
+  __syncthreads();
+  {  // pass 2: final ids
+    const int n = s_nimg;
+    int run = pre_mask, k = min(pre_start, n);
+    for (int t = c0; t < c1; ++t) {
+      const bool m = rm[t] != 0;
+      run += m;
+      while (k < n && s_start[k] <= t) ++k;   // images started at or before t
+      long long v0, v1;
+      if (k > 0 && t < s_start[k - 1] + P) {
+        const int p = t - s_start[k - 1];
+        v0 = s_base[k - 1] + p / g, v1 = s_base[k - 1] + p % g;
+      } else {
+        v0 = v1 = (m ? run - 1 : 0) + (k > 0 ? s_shift[k - 1] : 0);
+      }
+      ro[2 * (int64_t)t] = v0;
+      ro[2 * (int64_t)t + 1] = v1;
+    }
+  }
+}
+
+}  // namespace mm
+
+extern "C" int mm_position_ids(const int64_t* input_ids, const void* attention_mask, int mask_is_u8, int64_t batch,
+                               int64_t seq, int64_t attachment_id, int64_t tokens_per_image, int64_t grid, int use_2d,
+                               int64_t* out, int32_t* status, void* stream) {
+  using namespace mm;
+  if (batch < 0 || seq < 0 || seq > INT32_MAX / 4) return MM_ERR_BAD_ARG;
+  if (batch == 0 || seq == 0) return MM_OK;
+  if (!attention_mask || !out || (use_2d && (!input_ids || grid <= 0 || tokens_per_image != grid * grid)))
+    return MM_ERR_BAD_ARG;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (mask_is_u8)
+    position_ids_kernel<uint8_t><<<(unsigned)batch, kPosThreads, 0, st>>>(
+        input_ids, reinterpret_cast<const uint8_t*>(attention_mask), out, (int)seq, attachment_id, (int)tokens_per_image,
+        (int)grid, use_2d, status);
+  else
+    position_ids_kernel<int64_t><<<(unsigned)batch, kPosThreads, 0, st>>>(
+        input_ids, reinterpret_cast<const int64_t*>(attention_mask), out, (int)seq, attachment_id, (int)tokens_per_image,
+        (int)grid, use_2d, status);
+  MM_CUDA_CHECK(cudaGetLastError());
+  return MM_OK;
+}

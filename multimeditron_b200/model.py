@@ -99,5 +99,19 @@ class B200MultiModalEmbedder(torch.nn.Module):
                 ops.splice_scatter_idx(embedded, proj2d.contiguous(), bi, tr, status=st)  # :441-444
         return embedded
 
+    @torch.no_grad()
+    def position_ids(self, input_ids: torch.Tensor, attention_mask: torch.Tensor, use_2d: bool = False,
+                     modality: str = "image") -> torch.Tensor:
+        """The collator's `position_ids` (data_loader.py:155-188) built on the device from the ids and the mask:
+        [B,S] int64, or [B,S,2] with the image grid ids when `use_2d` (tokens per image / grid from the modality)."""
+        dev = self.embed_table.device
+        ids, mask = input_ids.to(dev, non_blocking=True), attention_mask.to(dev, non_blocking=True)
+        if not use_2d:
+            return ops.position_ids(mask)
+        m = self._get_modality_by_name(modality)
+        P = m._num_patches_per_entry
+        g = int(round(P ** 0.5))
+        return ops.position_ids(mask, ids, self.attachment_token_idx, P, g, use_2d=True, status=self.status())
+
     def forward(self, input_ids: torch.Tensor, processed_multimodal_inputs: Dict[str, Any], **kw) -> torch.Tensor:
         return self.embed_modalities_with_text(input_ids, processed_multimodal_inputs, **kw)

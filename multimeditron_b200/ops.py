@@ -355,6 +355,30 @@ def weighted_expert_sum(x: torch.Tensor, w: torch.Tensor, perm: torch.Tensor | N
     return out
 
 
+def position_ids(attention_mask: torch.Tensor, input_ids: torch.Tensor | None = None, attachment_id: int = -1,
+                 tokens_per_image: int = 0, grid: int = 0, use_2d: bool = False,
+                 status: torch.Tensor | None = None) -> torch.Tensor:
+    """data_loader.py:155-188 on the device: [B,S] int64 (1-D) or [B,S,2] int64 (2-D image position ids)."""
+    _cuda(attention_mask, input_ids, status)
+    lib = _lib.load()
+    B, S = attention_mask.shape
+    m = attention_mask.contiguous()
+    if m.dtype == torch.bool:
+        m = m.view(torch.uint8)
+    if m.dtype not in (torch.int64, torch.uint8):
+        raise TypeError(f"attention_mask must be int64, uint8 or bool, got {m.dtype}")
+    ids = None
+    if use_2d:
+        assert input_ids is not None and input_ids.dtype == torch.int64 and input_ids.shape == attention_mask.shape
+        ids = input_ids.contiguous()
+    out = torch.empty((B, S, 2) if use_2d else (B, S), dtype=torch.int64, device=m.device)
+    with _timed("mm_position_ids", float(B) * S * (8 + 8 * (2 if use_2d else 1))):
+        rc = lib.mm_position_ids(_ptr(ids), _ptr(m), int(m.dtype == torch.uint8), B, S, int(attachment_id),
+                                 int(tokens_per_image), int(grid), int(use_2d), _ptr(out), _ptr(status), _stream())
+    _check(rc, "mm_position_ids")
+    return out
+
+
 # --------------------------------------------------------------------------------- image pre-processing
 def preprocess_images(src: torch.Tensor, desc: torch.Tensor, size: int, kmax: int, max_h: int, max_w: int,
                       tmp_bytes: int, mean255, std255, out_dtype=torch.float32) -> torch.Tensor:

@@ -256,6 +256,69 @@ def gen_splice(ref):
     np.savez_compressed(os.path.join(GOLD, "token_range.npz"), **tr_out)
 
 
+POSITION_CASES = [  # name, batch, seq, images/row, grid, padding, min_len
+    ("right_1img", 3, 40, 1, 3, "right", 24), ("left_3img", 4, 64, 3, 3, "left", 40), ("noimg", 2, 20, 0, 3, "right", 9),
+    ("edges", 2, 22, 2, 3, "right", 22), ("grid4_left", 3, 60, 2, 4, "left", 45),
+]
+
+
+def gen_position_ids(ref):
+    """Runs the UNMODIFIED second half of DataCollatorForMultimodal.torch_call (data_loader.py:120-195); only the
+    tokenisation front half (SamplePreprocessor / loaders, not on the path) is replaced by pre-built features."""
+    from unittest import mock
+    dl = ref.data_loader
+    out = {}
+    for name, B, S, n_img, g, side, min_len in POSITION_CASES:
+        tpi = g * g
+        ids, mask = synth.make_sequences(B, S, n_img, tpi, VOCAB, ATT, START, END, PAD, seed=len(name), padding_side=side,
+                                         min_len=min_len)
+        if name == "edges":   # image block at position 0 of row 0 and flush at the end of row 1 (the `s > 0` quirk, :178)
+            blk = torch.tensor([START] + [ATT] * tpi + [END])
+            ids[0] = torch.cat([blk[1:], torch.full((S - len(blk) + 1,), 13)])        # attachment run starts at t = 0
+            ids[1] = torch.cat([torch.full((S - 2 * len(blk),), 17), blk, blk])
+            mask[:] = True
+        ranges = [splice_oracle.compute_token_range(ids[b].numpy(), [tpi] * (int((ids[b] == ATT).sum()) // tpi), ATT)
+                  for b in range(B)]
+        res = {}
+        for use_2d in (False, True):
+            feats = []
+            for b in range(B):
+                mods = []
+                for (s0, e0) in ranges[b]:
+                    pm = {"type": "image", "value": torch.zeros(1), "token_range": (s0, e0), "num_embeddings": tpi}
+                    if use_2d:   # what ImageProcessor.process emits with use_2d_position_ids (image_modality.py:99-108)
+                        pm["position_ids"] = torch.stack(torch.meshgrid(
+                            torch.arange(g, dtype=torch.long), torch.arange(g, dtype=torch.long), indexing="ij"),
+                            dim=-1).reshape(tpi, 2)
+                    mods.append(pm)
+                feats.append({"input_ids": ids[b].clone(), "labels": ids[b].clone(),
+                              "attention_mask": mask[b].long(), "modalities": mods})
+            fake_sp = mock.MagicMock()
+            fake_sp.return_value.process_modality_to_tensor.side_effect = lambda raw: raw
+            fake_sp.return_value.tokenize.side_effect = lambda processed, add_generation_prompt=False: processed
+            with mock.patch.object(dl, "SamplePreprocessor", fake_sp), \
+                    mock.patch.object(dl.BaseModalityLoader, "load_modalities", staticmethod(lambda f, loaders: f)):
+                coll = dl.DataCollatorForMultimodal(tokenizer=None, modality_processors={}, modality_loaders={},
+                                                    attachment_token="<att>", chat_template=None,
+                                                    use_2d_position_ids=use_2d)
+                batch = coll.torch_call(feats)
+            got = batch["position_ids"].numpy()
+            want = splice_oracle.position_ids(mask.numpy(), ranges, g, use_2d)
+            assert got.dtype == np.int64 and np.array_equal(got, want), f"position_ids oracle != reference ({name}, 2d={use_2d})"
+            res["2d" if use_2d else "1d"] = got
+            if not use_2d:   # the collator's index build, again from the real statements
+                ob, ot = splice_oracle.collator_indices(ranges)
+                pmi = batch["processed_multimodal_inputs"]
+                if ob.size:
+                    assert np.array_equal(pmi["batch_idx"]["image"].numpy(), ob)
+                    assert np.array_equal(pmi["token_range"]["image"].numpy(), ot)
+        out[name + "__ids"], out[name + "__mask"] = ids.numpy(), mask.numpy()
+        out[name + "__grid"] = np.int64(g)
+        out[name + "__pos1d"], out[name + "__pos2d"] = res["1d"], res["2d"]
+        print(f"[position_ids {name}] {tuple(ids.shape)} grid {g}: 1-D and 2-D pinned against the reference collator")
+    np.savez_compressed(os.path.join(GOLD, "position_ids.npz"), **out)
+
+
 MOE_CASES = [  # name, per-expert projector, fusion, experts, hidden, batch, weight seed, pixel seed
     ("moe_shared_avg", False, "weighted_average", 3, 64, 3, 21, 5),
     ("moe_shared_append", False, "sequence_append", 3, 64, 2, 22, 6),
@@ -340,6 +403,8 @@ def main():
         gen_modality(ref)
     if not only or "siglip" in only:
         gen_siglip()
+    if not only or "position_ids" in only:
+        gen_position_ids(ref)
     if not only or "preprocess" in only:
         gen_preprocess()
     if not only or "moe" in only:

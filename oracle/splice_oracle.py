@@ -64,3 +64,25 @@ def splice_rows_numpy(dest_bytes: np.ndarray, src_bytes: np.ndarray, dest_rows: 
     """Byte-level row scatter (used as the timed CPU baseline of the splice): dest[dest_rows[k]] = src[k]."""
     dest_bytes[dest_rows] = src_bytes
     return dest_bytes
+
+
+def position_ids(attention_mask: np.ndarray, token_ranges_per_sample, grid: int, use_2d: bool) -> np.ndarray:
+    """data_loader.py:155-188: `cumsum(mask) - 1`, zero where masked; with use_2d_position_ids every image's tokens get
+    (row, col) grid ids offset by the position at its first token, and everything after the image is shifted by
+    (largest id of the image's last token) - (1-D id of its last token; 0 when the image starts the row, :178)."""
+    m = np.asarray(attention_mask).astype(np.int64)
+    pos = np.cumsum(m, -1) - 1
+    pos[m == 0] = 0
+    if not use_2d:
+        return pos
+    pos = np.repeat(pos[..., None], 2, -1)
+    ii, jj = np.meshgrid(np.arange(grid), np.arange(grid), indexing="ij")
+    grid_ids = np.stack([ii, jj], -1).reshape(grid * grid, 2).astype(np.int64)   # image_modality.py:101-108
+    for b, ranges in enumerate(token_ranges_per_sample):
+        for (s, e) in ranges:
+            old_last = pos[b, e - 1].copy() if s > 0 else np.zeros(2, np.int64)
+            mod = grid_ids + pos[b, s][None, :]
+            next_last = np.full(2, mod[-1].max())
+            pos[b, s:e] = mod
+            pos[b, e:] += (next_last - old_last)[None, :]
+    return pos
