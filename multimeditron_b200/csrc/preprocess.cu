@@ -152,22 +152,37 @@ __global__ void __launch_bounds__(256) resize_rows_kernel(const uint8_t* __restr
   const int32_t* bounds = p.bounds + ((int64_t)img * 2 + 1) * S * 2;
   const int16_t* wts = p.w + ((int64_t)img * 2 + 1) * S * kmax;
   uint8_t* out = tmp + d[D_TMP];
-  for (int t = threadIdx.x; t < ROWS_PER_CTA * S; t += blockDim.x) {
-    const int r = t / S, x = t - r * S, y = y0 + r;
-    if (y >= H) break;
-    const int off = (int)(((uintptr_t)(base + ((int64_t)y * W + c_lo) * 3)) & 3);
+  // thread <-> output column: its taps are fetched once and applied to the CTA's 4 staged rows
+  int roff[ROWS_PER_CTA];
+#pragma unroll
+  for (int r = 0; r < ROWS_PER_CTA; ++r)
+    roff[r] = r * row_pitch + (int)(((uintptr_t)(base + ((int64_t)(y0 + r) * W + c_lo) * 3)) & 3) - c_lo * 3;
+  const int nrows = min(ROWS_PER_CTA, H - y0);
+  const int half = 1 << (shift - 1);
+  for (int x = threadIdx.x; x < S; x += blockDim.x) {
     const int xmin = bounds[2 * x], n = bounds[2 * x + 1];
-    const uint8_t* s = srow + r * row_pitch + off + (xmin - c_lo) * 3;
-    const int16_t* w = wts + (int64_t)x * kmax;
-    int a0 = 1 << (shift - 1), a1 = a0, a2 = a0;
+    const int16_t* w = wts + x * kmax;
+    int acc[ROWS_PER_CTA][3];
+#pragma unroll
+    for (int r = 0; r < ROWS_PER_CTA; ++r) acc[r][0] = acc[r][1] = acc[r][2] = half;
+    const int s0 = xmin * 3;
     for (int j = 0; j < n; ++j) {
       const int wj = w[j];
-      a0 += wj * s[3 * j]; a1 += wj * s[3 * j + 1]; a2 += wj * s[3 * j + 2];
+#pragma unroll
+      for (int r = 0; r < ROWS_PER_CTA; ++r) {
+        const uint8_t* s = srow + roff[r] + s0 + 3 * j;   // rows past the image read stale smem; never stored
+        acc[r][0] += wj * s[0]; acc[r][1] += wj * s[1]; acc[r][2] += wj * s[2];
+      }
     }
-    uint8_t* o = out + ((int64_t)y * S + x) * 3;
-    o[0] = (uint8_t)min(max(a0 >> shift, 0), 255);
-    o[1] = (uint8_t)min(max(a1 >> shift, 0), 255);
-    o[2] = (uint8_t)min(max(a2 >> shift, 0), 255);
+#pragma unroll
+    for (int r = 0; r < ROWS_PER_CTA; ++r) {
+      if (r < nrows) {
+        uint8_t* o = out + ((int64_t)(y0 + r) * S + x) * 3;
+        o[0] = (uint8_t)min(max(acc[r][0] >> shift, 0), 255);
+        o[1] = (uint8_t)min(max(acc[r][1] >> shift, 0), 255);
+        o[2] = (uint8_t)min(max(acc[r][2] >> shift, 0), 255);
+      }
+    }
   }
 }
 
@@ -204,6 +219,59 @@ __global__ void __launch_bounds__(256) resize_cols_norm_kernel(const int64_t* __
   o[2 * plane] = (OutT)__fdiv_rn(__fsub_rn(v2, m2), s2);
 }
 
+// Vertical pass, 4 horizontally adjacent pixels per thread (S % 4 == 0): 12 contiguous bytes per tap arrive as three
+// aligned 32-bit loads, the row's taps are shared by the 4 pixels, each plane gets one 8- or 16-byte store.
+template <typename OutT>
+__global__ void __launch_bounds__(256) resize_cols_norm4_kernel(const int64_t* __restrict__ desc, const void* ws,
+                                                                const uint8_t* __restrict__ tmp, OutT* __restrict__ out, int B,
+                                                                int S, int kmax, float m0, float m1, float m2, float s0,
+                                                                float s1, float s2) {
+  const int img = blockIdx.y;
+  const int S4 = S >> 2;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= S * S4) return;
+  const int y = t / S4, x = (t - y * S4) * 4;
+  const int64_t* d = desc + (int64_t)img * D_N;
+  PreWs p = carve(const_cast<void*>(ws), B, S, kmax);
+  const int shift = p.meta[((int64_t)img * 2 + 0) * 4];
+  const int32_t* bd = p.bounds + (((int64_t)img * 2 + 0) * S + y) * 2;
+  const int ymin = bd[0], n = bd[1];
+  const int16_t* w = p.w + (((int64_t)img * 2 + 0) * S + y) * kmax;
+  const uint32_t* s = reinterpret_cast<const uint32_t*>(tmp + d[D_TMP] + ((int64_t)ymin * S + x) * 3);
+  const int pitch = (S * 3) >> 2;   // 32-bit words per intermediate row
+  int acc[12];
+#pragma unroll
+  for (int i = 0; i < 12; ++i) acc[i] = 1 << (shift - 1);
+  for (int j = 0; j < n; ++j) {
+    const int wj = w[j];
+    const uint32_t u0 = __ldg(s + j * pitch), u1 = __ldg(s + j * pitch + 1), u2 = __ldg(s + j * pitch + 2);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      acc[i] += wj * (int)((u0 >> (8 * i)) & 0xff);
+      acc[4 + i] += wj * (int)((u1 >> (8 * i)) & 0xff);
+      acc[8 + i] += wj * (int)((u2 >> (8 * i)) & 0xff);
+    }
+  }
+  // acc[3*px + c]: byte order r0 g0 b0 r1 g1 b1 ...
+  const float mean[3] = {m0, m1, m2}, stdv[3] = {s0, s1, s2};
+  const int64_t plane = (int64_t)S * S;
+  OutT* o = out + (int64_t)img * 3 * plane + (int64_t)y * S + x;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    float v[4];
+#pragma unroll
+    for (int px = 0; px < 4; ++px)
+      v[px] = __fdiv_rn(__fsub_rn((float)min(max(acc[3 * px + c] >> shift, 0), 255), mean[c]), stdv[c]);
+    if (sizeof(OutT) == 4) {
+      *reinterpret_cast<float4*>(o + c * plane) = make_float4(v[0], v[1], v[2], v[3]);
+    } else {
+      uint2 q;
+      q.x = pack_bf16x2(v[0], v[1]), q.y = pack_bf16x2(v[2], v[3]);
+      *reinterpret_cast<uint2*>(o + c * plane) = q;
+    }
+  }
+}
+
 }  // namespace mm
 
 extern "C" int64_t mm_preprocess_workspace_bytes(int64_t B, int64_t S, int64_t kmax) {
@@ -227,8 +295,22 @@ extern "C" int mm_preprocess_images(const void* src, const int64_t* desc, int64_
   if (smem > 48 * 1024)
     MM_CUDA_CHECK(cudaFuncSetAttribute(resize_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   resize_weights_kernel<<<dim3((unsigned)B, 2), 256, 0, st>>>(desc, ws, (int)B, (int)S, (int)kmax);
-  resize_rows_kernel<<<dim3((unsigned)((max_h + ROWS_PER_CTA - 1) / ROWS_PER_CTA), (unsigned)B), 256, smem, st>>>(
+  resize_rows_kernel<<<dim3((unsigned)((max_h + ROWS_PER_CTA - 1) / ROWS_PER_CTA), (unsigned)B), 128, smem, st>>>(
       (const uint8_t*)src, desc, ws, (uint8_t*)tmp, (int)B, (int)S, (int)kmax, row_pitch);
+  const bool vec4 = (S % 4 == 0) && (((uintptr_t)tmp | (uintptr_t)out) & 15) == 0;   // tmp offsets are multiples of S*3
+  if (vec4) {
+    dim3 g4((unsigned)((S * (S / 4) + 255) / 256), (unsigned)B);
+    if (out_dtype == MM_F32)
+      resize_cols_norm4_kernel<float><<<g4, 256, 0, st>>>(desc, ws, (const uint8_t*)tmp, (float*)out, (int)B, (int)S,
+                                                          (int)kmax, mean255[0], mean255[1], mean255[2], std255[0],
+                                                          std255[1], std255[2]);
+    else
+      resize_cols_norm4_kernel<__nv_bfloat16><<<g4, 256, 0, st>>>(desc, ws, (const uint8_t*)tmp, (__nv_bfloat16*)out,
+                                                                  (int)B, (int)S, (int)kmax, mean255[0], mean255[1],
+                                                                  mean255[2], std255[0], std255[1], std255[2]);
+    MM_CUDA_CHECK(cudaGetLastError());
+    return MM_OK;
+  }
   dim3 g((unsigned)((S * S + 255) / 256), (unsigned)B);
   if (out_dtype == MM_F32)
     resize_cols_norm_kernel<float><<<g, 256, 0, st>>>(desc, ws, (const uint8_t*)tmp, (float*)out, (int)B, (int)S, (int)kmax,

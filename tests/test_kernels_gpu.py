@@ -103,6 +103,7 @@ def test_gemm_modular_residual_and_strided_output():
     (577, 1024, 4096, 1, 1e-5, 3.0),      # CLIP-L fc1 + QuickGELU, rows with a large mean (cancellation in acc - mean*c)
     (729, 1152, 4304, 3, 1e-6, 0.5),      # SigLIP fc1 + tanh-GELU, 18 slots
     (130, 144, 480, 0, 1e-6, 0.0),        # widths that are not multiples of 64/128: partial last chunk
+    (600, 1024, 1024, 1, 1e-5, -40.0),    # "massive activation" rows: |mean| >> spread of most channels (E[x^2]-mean^2 in fp32)
 ])
 def test_gemm_layernorm_fold(M, D, N, act, eps, shift):
     """Producer GEMM (+bias +residual) emits per-chunk row statistics; consumer GEMM applies LayerNorm from them.
@@ -111,7 +112,8 @@ def test_gemm_layernorm_fold(M, D, N, act, eps, shift):
     a = torch.randn(M, 256, generator=g0).bfloat16().to(DEV)
     wo = (torch.randn(D, 256, generator=g0) * 0.05).bfloat16().to(DEV)
     bo = (torch.randn(D, generator=g0) * 0.1).bfloat16().to(DEV)
-    res = (torch.randn(M, D, generator=g0) * (1.0 + 4.0 * (torch.rand(1, D, generator=g0) > 0.97)) + shift).bfloat16().to(DEV)
+    outlier = 200.0 if abs(shift) > 10 else 4.0      # a few channels carry huge values, as in trained CLIP towers
+    res = (torch.randn(M, D, generator=g0) * (1.0 + outlier * (torch.rand(1, D, generator=g0) > 0.97)) + shift).bfloat16().to(DEV)
     stats = torch.zeros(M, ops.row_stats_slots(D), 2, device=DEV)   # contract: zero-initialised once
     assert ops.row_stats_slots(D) == 16
     x = ops.gemm_ln_bias_act(a, wo, bo, residual=res, stats_out=stats)
