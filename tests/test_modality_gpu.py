@@ -129,3 +129,29 @@ def test_clip_l14_336_layerwise_sanity():
     err, ref_err = (y - ref).abs().max().item(), (refb - ref).abs().max().item()
     print(f"[clip_l14_336] max-abs {err:.3e} (reference bf16 run: {ref_err:.3e}) max-abs/absmax {err / scale:.3e}")
     assert err <= 2.0 * ref_err and err / scale <= 2e-2
+
+
+def test_full_size_cfg2_batch_independence_and_splice_placement():
+    """BASELINE configs[1] at FULL size (256 images of 336 px, ViT-L/14-336 -> 4096, S = 642): size-independent
+    properties — (i) an image's embeddings do not depend on the batch it travels in (bit-exact vs a batch of 3),
+    (ii) every projected row lands exactly at its attachment position and every text row is the embedding row."""
+    cfg = TOWERS["clip_l14_336"]
+    m, _ = _modality("clip_l14_336", 4096, 0)
+    B, P, H, V = 256, cfg.num_patches, 4096, 5000
+    px = synth.make_pixels(cfg, B, seed=11).to(DEV)
+    y = m(px)                                                        # [256, 576, 4096]
+    pick = [0, 100, 255]
+    y3 = m(px[pick].contiguous())
+    assert torch.equal(y[pick], y3)
+    att, start, end, pad = V - 2, V - 4, V - 3, V - 1
+    S = P + 2 + 64
+    ids, _ = synth.make_sequences(B, S, 1, P, V - 4, att, start, end, pad, seed=5)
+    table = (torch.randn(V, H, generator=torch.Generator().manual_seed(2)) * 0.02).bfloat16().to(DEV)
+    e = B200MultiModalEmbedder(table, [m], att)
+    out = e(ids, {"stacked": {"image": px}, "batch_idx": {}, "token_range": {}}, positions_from="device")
+    e.check()
+    flat, idsd = out.view(B * S, H), ids.to(DEV).view(-1)
+    is_att = idsd == att
+    assert int(is_att.sum()) == B * P
+    assert torch.equal(flat[is_att], y.view(B * P, H))               # row-major order == collator order (model.py:443-444)
+    assert torch.equal(flat[~is_att], table[idsd[~is_att]])          # text rows untouched, bit-exact
