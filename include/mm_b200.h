@@ -161,6 +161,16 @@ int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, con
  * LN itself stays in fp32 — same error scale (2^-9 relative per operand), covered by the stated bf16 tolerance.
  */
 int64_t mm_gemm_row_stats_slots(int64_t N);
+
+/*
+ * mm_set_gemm_pair — tuning switch of mm_gemm_bias_act / mm_gemm_ln_bias_act (no reference counterpart).
+ * The GEMMs run by default (M > 128) on CTA PAIRS: the two CTAs of a 2-CTA cluster compute one 256 x 256 tile with
+ * tcgen05.mma.cta_group::2, each CTA staging its 128 rows of A and half of the W tile.  on = 0 forces the 1-CTA
+ * kernel (128 x 256 tiles), on = 1 the pair kernel, on < 0 returns to the default (environment MM_B200_GEMM_PAIR,
+ * else pair).  Both kernels accumulate every output in the same k order: results are bit-identical (tested).
+ * Process-wide, not thread-safe against concurrent GEMM launches.
+ */
+void mm_set_gemm_pair(int on);
 int mm_gemm_ln_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias,
                         void* C, int64_t ldc, int64_t M, int64_t N, int64_t K, int act,
                         const void* residual, int64_t ldr, const int32_t* out_row_map,

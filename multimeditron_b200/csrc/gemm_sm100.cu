@@ -1,8 +1,14 @@
 // gemm_sm100.cu — persistent warp-specialised tcgen05 GEMM:  C = act(A · Wᵀ + bias) [+ residual]
 //
-//   * operands bf16, K-major, staged by TMA (SWIZZLE_128B, 64-element K slabs) into a 4-deep smem ring
-//   * tcgen05.mma cta_group::1, UMMA 128x256x16, fp32 accumulators in TMEM, double-buffered
-//     (2 x 256 columns) so tile i+1's main loop overlaps tile i's epilogue
+//   * operands bf16, K-major, staged by TMA (SWIZZLE_128B, 64-element K slabs) into a shared-memory ring
+//   * CTA-pair variant (kPair, the default for M > 128): the two CTAs of a 2-CTA cluster compute one 256 x 256 tile
+//     with tcgen05.mma cta_group::2 (UMMA 256x256x16) issued by the leader CTA; each CTA stages its own 128 rows of
+//     A and HALF of the B tile, so shared-memory operand bytes per FLOP halve and the ring is 6 deep.
+//     Protocol: every TMA load of both CTAs signals the LEADER's full barrier; the leader's producer posts the
+//     bytes of both CTAs; tcgen05.commit multicasts to both CTAs' empty / tmem_full barriers; the peer's epilogue
+//     warps release the accumulator stage on the leader's tmem_empty barrier (mapa + remote arrive).
+//   * 1-CTA variant (small M, and the gather kernel): tcgen05.mma cta_group::1, UMMA 128x256x16, 4-deep ring
+//   * fp32 accumulators in TMEM, double-buffered (2 x 256 columns) so tile i+1's main loop overlaps tile i's epilogue
 //   * epilogue warps: tcgen05.ld -> bias/activation in fp32 -> bf16 -> per-warp swizzled smem
 //     transpose -> fully coalesced 16-byte row stores (optionally + residual, optional row remap /
 //     scatter map so that drop-CLS, CLS-insert and the splice into inputs_embeds cost no extra pass)
@@ -23,13 +29,13 @@ constexpr int BN = 256;
 constexpr int BK = 64;  // 64 bf16 = 128 B = one SWIZZLE_128B row
 constexpr int kUmmaK = 16;
 constexpr int kAStageBytes = BM * BK * 2;  // 16 KiB
-constexpr int kBStageBytes = BN * BK * 2;  // 32 KiB
+constexpr int kBStageBytes = BN * BK * 2;  // 32 KiB (CTA pair: each CTA holds half of it)
 constexpr int kEpiWarpBytes = 32 * 128;    // 32 rows x 64 bf16
 constexpr int kTmemCols = 512;
 constexpr int kKTableMax = 3072 + 64;  // patch-embed k -> pixel offset table (ints)
 
 constexpr int kStatSlots = 16;  // row-statistics slots per row: one 128-byte line, one slot per 128 output columns
-constexpr int kMaxStages = 4;
+constexpr int kMaxStages = 6;
 struct GemmSmemTail {
   uint64_t full[kMaxStages];
   uint64_t empty[kMaxStages];
@@ -40,17 +46,21 @@ struct GemmSmemTail {
 
 // TMA variant: 4 stages, 8 epilogue warps (2 per TMEM lane quadrant, each owning half of the 256 columns).
 // Gather variant (patch embed): 3 stages, 4 epilogue warps, 4 A-producer warps, + 12.5 KiB static k-offset table.
-template <bool kGatherA>
+// CTA-pair variant: 6 stages of (16 KiB A + 16 KiB half-B).
+template <bool kGatherA, bool kPair = false>
 struct GemmCfg {
-  static constexpr int kStages = kGatherA ? 3 : 4;
+  static_assert(!(kGatherA && kPair), "the gather kernel is 1-CTA");
+  static constexpr int kStages = kGatherA ? 3 : (kPair ? 6 : 4);
+  static constexpr int kBStage = kPair ? kBStageBytes / 2 : kBStageBytes;
   static constexpr int kEpiWarps = kGatherA ? 4 : 8;
   static constexpr int kChunksPerWarp = (BN / 64) / (kEpiWarps / 4);
   static constexpr int kThreads = 128 + kEpiWarps * 32 + (kGatherA ? 128 : 0);
   static constexpr int kEpiBytes = kEpiWarps * kEpiWarpBytes;
-  static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * (kAStageBytes + kBStageBytes) + kEpiBytes + 256;
+  static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * (kAStageBytes + kBStage) + kEpiBytes + 256;
 };
 static_assert(sizeof(GemmSmemTail) <= 256, "tail too large");
 static_assert(GemmCfg<false>::kSmemBytes <= 232448, "smem budget");
+static_assert(GemmCfg<false, true>::kSmemBytes <= 232448, "smem budget (pair)");
 static_assert(GemmCfg<true>::kSmemBytes + kKTableMax * 4 + kKTableMax / 8 <= 232448, "smem budget (gather)");
 
 struct GemmParams {
@@ -65,6 +75,7 @@ struct GemmParams {
   int map_in, map_out, map_off;  // formula row map: out_row = (m / map_in) * map_out + map_off + m % map_in
   int act;
   int tiles_m, tiles_n;
+  int pair;  // 1: CTA-pair kernel (256-row tiles; the B tensor map has a 128-row box)
   // LayerNorm folded into the GEMM (mm_gemm_ln_bias_act):  LN(x)·Wᵀ + b = rstd·(x·W''ᵀ) + b'
   // with W'' = gamma ⊙ W re-centred so that every row sums to zero (the mean term cancels inside the MMA).
   //   producer side: per 64-column chunk (sum, sum of squares) of the rows this GEMM writes
@@ -141,18 +152,19 @@ __device__ __forceinline__ float butterfly8(const float (&a)[8], int ch) {
 // LN: 0 = plain epilogue, 1 = also emits row statistics (stats_out), 2 = applies the folded LayerNorm (ln_stats),
 // 3 = plain with a modular residual row (res_mod > 0).
 // Compile-time, not run-time: each variant keeps the lean epilogue it needs (the epilogue is issue/i-cache bound).
-template <bool kGatherA, int ACT, int LN>
-__global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
+template <bool kGatherA, int ACT, int LN, bool kPair>
+__global__ void __launch_bounds__(GemmCfg<kGatherA, kPair>::kThreads, 1)
     gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                         const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  using Cfg = GemmCfg<kGatherA>;
+  using Cfg = GemmCfg<kGatherA, kPair>;
   constexpr int kStages = Cfg::kStages;
   constexpr int kEpiWarps = Cfg::kEpiWarps;
+  constexpr int kBStage = Cfg::kBStage;
   uint8_t* sA = smem;
   uint8_t* sB = smem + kStages * kAStageBytes;
-  uint8_t* sEpi = sB + kStages * kBStageBytes;
+  uint8_t* sEpi = sB + kStages * kBStage;
   GemmSmemTail* tail = reinterpret_cast<GemmSmemTail*>(sEpi + Cfg::kEpiBytes);
   __shared__ int s_koff[kGatherA ? kKTableMax : 1];
   __shared__ uint8_t s_kcontig[kGatherA ? kKTableMax / 8 : 1];  // 1: the 8 pixels of this k-group are consecutive in memory
@@ -161,6 +173,13 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
   const int lane = threadIdx.x & 31;
   const int num_kb = (p.K + BK - 1) / BK;
   const int num_tiles = p.tiles_m * p.tiles_n;
+  // CTA pair: a tile is 256 rows (p.tiles_m counts those), this CTA owns rows [rank*128, +128) and the B rows
+  // [rank*128, +128) of it; tiles are strided over PAIRS.
+  const uint32_t rank = kPair ? cluster_ctarank() : 0u;
+  constexpr int kTileRows = kPair ? 2 * BM : BM;
+  const int m_off = (int)rank * BM;
+  const int tile0 = kPair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int tile_step = kPair ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
   if (warp == 0 && lane == 0) {
     if (!kGatherA) tma_prefetch_desc(&tmA);
@@ -173,13 +192,18 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tail->tmem_full[i], 1);
-      mbar_init(&tail->tmem_empty[i], kEpiWarps);
+      mbar_init(&tail->tmem_empty[i], kPair ? 2 * kEpiWarps : kEpiWarps);  // pair: both CTAs' warps, leader's barrier
     }
     fence_barrier_init();
   }
+  if (kPair) cluster_sync_all();  // the peer's barriers exist before anything can signal them
   if (warp == 2) {
-    tmem_alloc(&tail->tmem_base, kTmemCols);
-    tmem_relinquish();
+    if (kPair) {
+      tmem_alloc_pair(&tail->tmem_base, kTmemCols);
+    } else {
+      tmem_alloc(&tail->tmem_base, kTmemCols);
+      tmem_relinquish();
+    }
   }
   if (kGatherA) {
     // k -> pixel offset table (c*img*img + ky*img + kx); -1 for the zero padding beyond k_real
@@ -200,7 +224,7 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
     }
   }
   tc_fence_before();
-  __syncthreads();
+  if (kPair) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tail->tmem_base;
 
@@ -209,17 +233,21 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
     if (elect_one_sync()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        const int m0 = (t / p.tiles_n) * BM, n0 = (t % p.tiles_n) * BN;
+      for (int t = tile0; t < num_tiles; t += tile_step) {
+        const int m0 = (t / p.tiles_n) * kTileRows + m_off, n0 = (t % p.tiles_n) * BN + (kPair ? m_off : 0);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&tail->empty[stage], phase ^ 1);
-          if (kGatherA) {
+          if (kPair) {
+            if (rank == 0) mbar_arrive_expect_tx(&tail->full[stage], 2 * (kAStageBytes + kBStage));
+            tma_load_2d_pair(sA + stage * kAStageBytes, &tmA, &tail->full[stage], kb * BK, m0);
+            tma_load_2d_pair(sB + stage * kBStage, &tmB, &tail->full[stage], kb * BK, n0);
+          } else if (kGatherA) {
             mbar_arrive_expect_tx(&tail->full[stage], kBStageBytes);
           } else {
             mbar_arrive_expect_tx(&tail->full[stage], kAStageBytes + kBStageBytes);
             tma_load_2d(sA + stage * kAStageBytes, &tmA, &tail->full[stage], kb * BK, m0);
           }
-          tma_load_2d(sB + stage * kBStageBytes, &tmB, &tail->full[stage], kb * BK, n0);
+          if (!kPair) tma_load_2d(sB + stage * kBStageBytes, &tmB, &tail->full[stage], kb * BK, n0);
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
@@ -229,13 +257,13 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
     }
   } else if (warp == 1) {
     // =========================== MMA issuer (single thread) ===========================
-    if (elect_one_sync()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, 0, 0);
+    if (rank == 0 && elect_one_sync()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kTileRows, BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int t = tile0; t < num_tiles; t += tile_step) {
         mbar_wait(&tail->tmem_empty[as], aphase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
@@ -243,20 +271,23 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
           mbar_wait(&tail->full[stage], phase);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(sA + stage * kAStageBytes);
-          const uint32_t b_addr = smem_u32(sB + stage * kBStageBytes);
+          const uint32_t b_addr = smem_u32(sB + stage * kBStage);
 #pragma unroll
           for (int k = 0; k < BK / kUmmaK; ++k) {
             const uint64_t da = umma_desc_sw128(a_addr + k * kUmmaK * 2, 16, 1024);
             const uint64_t db = umma_desc_sw128(b_addr + k * kUmmaK * 2, 16, 1024);
-            tc_mma_f16_ss(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            if (kPair) tc_mma_f16_ss_pair(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            else tc_mma_f16_ss(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
           }
-          tc_commit(&tail->empty[stage]);  // frees the smem slot when these MMAs retire
+          // frees the smem slot (pair: in both CTAs) when these MMAs retire
+          if (kPair) tc_commit_pair(&tail->empty[stage]); else tc_commit(&tail->empty[stage]);
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        tc_commit(&tail->tmem_full[as]);  // accumulator ready for the epilogue
+        // accumulator ready for the epilogue (pair: both CTAs' halves)
+        if (kPair) tc_commit_pair(&tail->tmem_full[as]); else tc_commit(&tail->tmem_full[as]);
         if (++as == 2) {
           as = 0;
           aphase ^= 1;
@@ -277,7 +308,7 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
     constexpr bool fold_mode = !kGatherA && LN == 2;
     constexpr int ln_slots = kStatSlots;
     auto load_stats = [&](int tile) {
-      const int mb = (tile / p.tiles_n) * BM + q * 32 + (lane >> 3);
+      const int mb = (tile / p.tiles_n) * kTileRows + m_off + q * 32 + (lane >> 3);
 #pragma unroll
       for (int it = 0; it < 8; ++it) {
         const int gm = mb + it * 4;
@@ -286,9 +317,9 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
           rv[it] = __ldg(reinterpret_cast<const int4*>(p.ln_stats + (int64_t)gm * ln_slots) + (lane & 7));
       }
     };
-    if (fold_mode) load_stats(blockIdx.x);
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-      const int m0 = (t / p.tiles_n) * BM, n0 = (t % p.tiles_n) * BN;
+    if (fold_mode) load_stats(tile0);
+    for (int t = tile0; t < num_tiles; t += tile_step) {
+      const int m0 = (t / p.tiles_n) * kTileRows + m_off, n0 = (t % p.tiles_n) * BN;
       // destination row of this lane's GEMM row
       const int my_m = m0 + q * 32 + lane;
       int my_out = -1;
@@ -321,7 +352,7 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
         const float mean = s1 * p.ln_inv_k;
         const float var = fmaxf(s2 * p.ln_inv_k - mean * mean, 0.f);
         ln_rstd = rsqrtf(var + p.ln_eps);
-        load_stats(t + (int)gridDim.x);   // rv is free again: request the next tile's lines now
+        load_stats(t + tile_step);   // rv is free again: request the next tile's lines now
       }
       mbar_wait(&tail->tmem_full[as], aphase);
       tc_fence_after();
@@ -433,7 +464,10 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
       // all TMEM reads of this accumulator stage are complete (tc_wait_ld above)
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tail->tmem_empty[as]);
+      if (lane == 0) {
+        if (kPair) mbar_arrive_cta(&tail->tmem_empty[as], 0);   // the leader's MMA thread owns the accumulator ring
+        else mbar_arrive(&tail->tmem_empty[as]);
+      }
       if (++as == 2) {
         as = 0;
         aphase ^= 1;
@@ -447,7 +481,7 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
     const __nv_bfloat16* px16 = reinterpret_cast<const __nv_bfloat16*>(p.pixels);
     int stage = 0;
     uint32_t phase = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+    for (int t = tile0; t < num_tiles; t += tile_step) {
       const int m0 = (t / p.tiles_n) * BM;
       const int m = m0 + row;
       int64_t base = -1;
@@ -514,11 +548,12 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA>::kThreads, 1)
     }
   }
 
+  // pair: nobody leaves (or frees TMEM) while the pair's MMAs / multicast commits can still touch this CTA
   tc_fence_before();
-  __syncthreads();
+  if (kPair) cluster_sync_all(); else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, kTmemCols);
+    if (kPair) tmem_dealloc_pair(tmem_base, kTmemCols); else tmem_dealloc(tmem_base, kTmemCols);
   }
 }
 
@@ -608,25 +643,52 @@ int make_tmap_3d_sw32(CUtensorMap* tm, const void* ptr, int64_t d0, int64_t d1, 
   return MM_OK;
 }
 
-template <bool kGatherA, int ACT, int LN = 0>
-static int launch_gemm_inst(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
-  using Cfg = GemmCfg<kGatherA>;
+template <bool kGatherA, int ACT, int LN, bool kPair>
+static int launch_gemm_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
+  using Cfg = GemmCfg<kGatherA, kPair>;
   static bool attr_set[64] = {false};
   int dev = 0;
   MM_CUDA_CHECK(cudaGetDevice(&dev));
+  auto* kern = gemm_bf16_tn_kernel<kGatherA, ACT, LN, kPair>;
   if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-    MM_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_tn_kernel<kGatherA, ACT, LN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       Cfg::kSmemBytes));
+    MM_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     attr_set[dev] = true;
   }
-  p.tiles_m = (p.M + BM - 1) / BM;
+  constexpr int kTileRows = kPair ? 2 * BM : BM;
+  p.tiles_m = (p.M + kTileRows - 1) / kTileRows;
   p.tiles_n = (p.N + BN - 1) / BN;
   const int tiles = p.tiles_m * p.tiles_n;
-  const int sms = sm_count();
-  const int grid = tiles < sms ? tiles : sms;
-  gemm_bf16_tn_kernel<kGatherA, ACT, LN><<<grid, Cfg::kThreads, Cfg::kSmemBytes, st>>>(tmA, tmB, p);
-  MM_CUDA_CHECK(cudaGetLastError());
+  const int units = kPair ? sm_count() / 2 : sm_count();   // persistent: one CTA (or CTA pair) per SM (TPC)
+  const int grid = (tiles < units ? tiles : units) * (kPair ? 2 : 1);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid), cfg.blockDim = dim3(Cfg::kThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes, cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2, attr[0].val.clusterDim.y = 1, attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr, cfg.numAttrs = kPair ? 1 : 0;
+  MM_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, (const GemmParams)p));
   return MM_OK;
+}
+
+// CTA-pair kernel on/off: mm_set_gemm_pair(), else the environment (MM_B200_GEMM_PAIR=0 forces the 1-CTA kernel
+// everywhere — A/B measurements and the pair-vs-single parity test), else on.
+static int g_pair_override = -1;
+static bool pair_enabled() {
+  if (g_pair_override >= 0) return g_pair_override != 0;
+  static const bool on = [] {
+    const char* e = getenv("MM_B200_GEMM_PAIR");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
+template <bool kGatherA, int ACT, int LN = 0>
+static int launch_gemm_inst(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
+  if constexpr (!kGatherA) {
+    if (p.pair) return launch_gemm_cfg<false, ACT, LN, true>(tmA, tmB, p, st);
+  }
+  return launch_gemm_cfg<kGatherA, ACT, LN, false>(tmA, tmB, p, st);
 }
 
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
@@ -678,9 +740,11 @@ static int gemm_entry(const void* A, int64_t lda, const void* W, int64_t ldw, co
   CUtensorMap tmA, tmB;
   int rc = make_tmap_2d(&tmA, A, M, K, lda, BM);
   if (rc != MM_OK) return rc;
-  rc = make_tmap_2d(&tmB, W, N, K, ldw, BN);
+  const bool pair = M > BM && pair_enabled();   // at most one row tile: the peer CTA would only see padding
+  rc = make_tmap_2d(&tmB, W, N, K, ldw, pair ? BN / 2 : BN);
   if (rc != MM_OK) return rc;
   GemmParams p{};
+  p.pair = pair ? 1 : 0;
   p.C = reinterpret_cast<__nv_bfloat16*>(C);
   p.bias = reinterpret_cast<const __nv_bfloat16*>(bias);
   p.residual = reinterpret_cast<const __nv_bfloat16*>(residual);
@@ -709,6 +773,8 @@ extern "C" int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64
   return gemm_entry(A, lda, W, ldw, bias, C, ldc, M, N, K, act, residual, ldr, res_mod, res_row_off, out_row_map,
                     n_out_rows, nullptr, nullptr, 0.f, stream);
 }
+
+extern "C" void mm_set_gemm_pair(int on) { g_pair_override = on < 0 ? -1 : (on ? 1 : 0); }
 
 extern "C" int64_t mm_gemm_row_stats_slots(int64_t N) { return (N > 0 && N <= 128 * kStatSlots) ? kStatSlots : -1; }
 

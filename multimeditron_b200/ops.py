@@ -274,6 +274,11 @@ def gemm_ln_bias_act(a: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None
     return out
 
 
+def set_gemm_pair(on: int) -> None:
+    """0: 1-CTA GEMM kernel, 1: CTA-pair (cta_group::2) kernel, -1: default (pair for M > 128).  Results are bit-identical."""
+    _lib.load().mm_set_gemm_pair(int(on))
+
+
 def row_stats_slots(n: int) -> int:
     return int(_lib.load().mm_gemm_row_stats_slots(n))
 

@@ -144,6 +144,41 @@ def test_gemm_layernorm_fold(M, D, N, act, eps, shift):
     assert torch.equal(y, y_again)                               # fixed summation order: bit-reproducible
 
 
+@pytest.mark.parametrize("M,N,K", [(129, 256, 64), (300, 264, 200), (1000, 1024, 1024), (2308, 3072, 1024),
+                                   (56_837, 512, 128), (4617, 4096, 1024)])
+def test_gemm_pair_kernel_bit_identical_to_single_cta(M, N, K):
+    """The CTA-pair kernel (cta_group::2, 256 x 256 tiles; default for M > 128) against the 1-CTA kernel: every epilogue
+    variant — plain, activation, residual + row map, statistics producer, LayerNorm-fold consumer — bit for bit."""
+    g0 = torch.Generator().manual_seed(M ^ N ^ K)
+    a = torch.randn(M, K, generator=g0).bfloat16().to(DEV)
+    w = (torch.randn(N, K, generator=g0) * 0.05).bfloat16().to(DEV)
+    bs = (torch.randn(N, generator=g0) * 0.5).bfloat16().to(DEV)
+    res = torch.randn(M, N, generator=g0).bfloat16().to(DEV)
+    perm = torch.randperm(M, generator=g0).int().to(DEV)
+    perm[::5] = -1
+    gamma, beta = (1 + 0.1 * torch.randn(K, generator=g0)).bfloat16().to(DEV), (0.1 * torch.randn(K, generator=g0)).bfloat16().to(DEV)
+    wf, bf = ops.fold_layernorm(w, bs, gamma, beta)
+    ln_stats = (torch.rand(M, 16, 2, generator=g0) * 64 + 0.5).to(DEV)
+    got = {}
+    try:
+        for pair in (0, 1):
+            ops.set_gemm_pair(pair)
+            o_map = torch.full((M, N), 7.0, device=DEV).bfloat16()
+            ops.gemm_bias_act(a, w, bs, 2, residual=res, out=o_map, out_row_map=perm)
+            outs = [ops.gemm_bias_act(a, w, None), ops.gemm_bias_act(a, w, bs, 1), o_map]
+            if N <= 2048:
+                st = torch.zeros(M, 16, 2, device=DEV)
+                outs += [ops.gemm_ln_bias_act(a, w, bs, residual=res, stats_out=st), st]
+            if K <= 2048:
+                outs.append(ops.gemm_ln_bias_act(a, wf, bf, act=1, ln_stats=ln_stats, eps=1e-5))
+            got[pair] = outs
+    finally:
+        ops.set_gemm_pair(-1)
+    for x, y in zip(got[0], got[1]):
+        assert torch.equal(x, y)
+    close(got[1][0], a.float() @ w.float().t())
+
+
 def test_gemm_rejects_bad_arguments():
     a = torch.zeros(16, 12, device=DEV).bfloat16()   # K % 8 != 0
     w = torch.zeros(16, 12, device=DEV).bfloat16()

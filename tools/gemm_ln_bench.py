@@ -1,5 +1,6 @@
 """Per-shape timing of the encoder GEMMs: plain vs stats-emitting vs LayerNorm-folded epilogues (cfg2 shapes).
-    python tools/gemm_ln_bench.py [images]        (set MM_B200_LIB=/path/to/other/libmm_b200.so to A/B a build)"""
+    python tools/gemm_ln_bench.py [images]        (set MM_B200_LIB=/path/to/other/libmm_b200.so to A/B a build;
+    MM_B200_GEMM_PAIR=0 times the 1-CTA kernel instead of the CTA-pair kernel)"""
 import sys, torch
 sys.path.insert(0, ".")
 from multimeditron_b200 import ops, _lib
