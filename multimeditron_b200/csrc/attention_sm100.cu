@@ -26,7 +26,7 @@
 namespace mm {
 
 constexpr int kBQ = 128;
-constexpr int kAttnThreads = 384;          // w0 TMA, w1 MMA, w2 TMEM alloc, w3 idle, w4-7 stream 0, w8-11 stream 1
+constexpr int kAttnThreads = 384;          // w0 TMA, w1 MMA stream 0, w2 TMEM alloc, w3 MMA stream 1, w4-7 / w8-11 softmax of stream 0 / 1
 constexpr float kRescaleThreshold = 8.0f;  // log2 units: P <= 2^8, harmless in bf16/fp32
 constexpr int kMaxStages = 8;
 #ifndef MM_ATTN_POLL_NS
@@ -283,49 +283,50 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
           if (!progress) __nanosleep(kPollSleepNs);  // leave the issue slots of this scheduler to the softmax warp
         }
       }
-    } else if (warp == 1) {
-      // =========================== MMA issuer (event loop over the two streams) ===========================
+    } else if (warp == 1 || warp == 3) {
+      // =========================== MMA issuers: warp 1 serves stream 0, warp 3 stream 1 ===========================
+      // (one thread polling the barriers of both streams reacted to each event in ~500-900 clk and was the pacing
+      // resource of the whole kernel; per-stream issuers halve the polling loop and never queue behind each other)
+      const int s_lo = warp == 1 ? 0 : 1;
       if (elect_one_sync()) {
         constexpr uint32_t idesc_s = umma_idesc_bf16(kBQ, BKV, 0, 0);
         constexpr uint32_t idesc_pv = umma_idesc_bf16(kBQ, 64, 0, 1);   // B (= V) is MN-major
         constexpr uint32_t idesc_pvx = umma_idesc_bf16(kBQ, 16, 0, 1);  // the 16 extra head columns
         TRACE_DECL
         // per-stream cursor: group, tile within group, next S / next PV kv step, and barrier use counts
-        int cg[2] = {0, 0}, cj[2] = {0, 0}, cnt[2], ks[2] = {0, 0}, kp[2] = {0, 0};
-        uint32_t n_tile[2] = {0, 0}, n_s[2] = {0, 0}, n_pv[2] = {0, 0};
-        cnt[0] = sc.ngroups ? sc.ntiles(0, 0) : 0;
-        cnt[1] = sc.ngroups ? sc.ntiles(1, 0) : 0;
+        const int s = s_lo;
+        int cg = 0, cj = 0, ks = 0, kp = 0;
+        uint32_t n_tile = 0, n_s = 0, n_pv = 0;
+        int cnt = sc.ngroups ? sc.ntiles(s, 0) : 0;
         auto slot_of = [&](int g, int kt, int& stage, uint32_t& phase) {
           const int seq = g * nkv + kt;
           const int r = seq / NS;
           stage = seq - r * NS;
           phase = (uint32_t)r & 1u;
         };
-        while (cg[0] < sc.ngroups || cg[1] < sc.ngroups) {
+        while (cg < sc.ngroups) {
           bool progress = false;
-#pragma unroll
-          for (int s = 0; s < 2; ++s) {
-            if (cg[s] >= sc.ngroups) continue;
+          {
             int stage;
             uint32_t phase;
-            if (cnt[s] == 0) {
+            if (cnt == 0) {
               // this stream has no query tile in the group: only hand its share of the K/V slots back
-              slot_of(cg[s], kp[s], stage, phase);
+              slot_of(cg, kp, stage, phase);
               if (mbar_test(&bars->kv_full[stage], phase)) {
                 mbar_arrive(&bars->kv_empty[stage]);
                 progress = true;
-                if (++kp[s] == nkv) {
-                  kp[s] = 0;
-                  if (++cg[s] < sc.ngroups) cnt[s] = sc.ntiles(s, cg[s]);
+                if (++kp == nkv) {
+                  kp = 0;
+                  if (++cg < sc.ngroups) cnt = sc.ntiles(s, cg);
                 }
               }
               continue;
             }
             // ---- S(ks) = Q K^T : needs Q (first step), the K/V slot, and the S accumulator back from the softmax
-            if (ks[s] < nkv) {
-              slot_of(cg[s], ks[s], stage, phase);
-              if ((ks[s] != 0 || mbar_test(&bars->q_full[s], n_tile[s] & 1)) &&
-                  mbar_test(&bars->kv_full[stage], phase) && mbar_test(&bars->s_empty[s], (n_s[s] & 1) ^ 1)) {
+            if (ks < nkv) {
+              slot_of(cg, ks, stage, phase);
+              if ((ks != 0 || mbar_test(&bars->q_full[s], n_tile & 1)) &&
+                  mbar_test(&bars->kv_full[stage], phase) && mbar_test(&bars->s_empty[s], (n_s & 1) ^ 1)) {
                 tc_fence_after();
                 progress = true;
                 const uint32_t q_addr = smem_u32(sQ + s * Cfg::kQMain);
@@ -343,22 +344,22 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
                 }
                 tc_commit(&bars->s_full[s]);
                 TRACE_MMA(6 + s);
-                ++n_s[s];
-                if (++ks[s] == nkv) tc_commit(&bars->q_empty[s]);  // Q tile free once these MMAs retire
+                ++n_s;
+                if (++ks == nkv) tc_commit(&bars->q_empty[s]);  // Q tile free once these MMAs retire
               }
             }
             // ---- O += P(kp) V : needs P from the softmax (and, for the first step, the drained O accumulator)
-            if (kp[s] < ks[s]) {
-              if (mbar_test(&bars->p_full[s], n_pv[s] & 1) &&
-                  (kp[s] != 0 || mbar_test(&bars->o_empty[s], (n_tile[s] & 1) ^ 1))) {
+            if (kp < ks) {
+              if (mbar_test(&bars->p_full[s], n_pv & 1) &&
+                  (kp != 0 || mbar_test(&bars->o_empty[s], (n_tile & 1) ^ 1))) {
                 tc_fence_after();
                 progress = true;
-                slot_of(cg[s], kp[s], stage, phase);
+                slot_of(cg, kp, stage, phase);
                 const uint32_t v_addr = smem_u32(sKV + stage * Cfg::kStageBytes + Cfg::kKMain);
                 const uint32_t vx_addr = smem_u32(sKV + stage * Cfg::kStageBytes + 2 * Cfg::kKMain + Cfg::kKX);
                 const uint32_t d = tmem_base + Cfg::kColO + s * HD;
                 const uint32_t a = tmem_base + Cfg::kColP + s * (BKV / 2);
-                const uint32_t acc0 = kp[s] != 0;
+                const uint32_t acc0 = kp != 0;
 #pragma unroll
                 for (int k = 0; k < BKV / 16; ++k) {
                   // A = P from TMEM (16 bf16 = 8 columns per k-step); B = V MN-major, 16 kv rows per k-step
@@ -369,20 +370,20 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
                 }
                 tc_commit(&bars->pv_done[s]);
                 TRACE_MMA(8 + s);
-                ++n_pv[s];
-                if (cj[s] == cnt[s] - 1) tc_commit(&bars->kv_empty[stage]);  // last tile of this stream on the slot
-                if (++kp[s] == nkv) {  // tile finished: next tile / next group
-                  ks[s] = kp[s] = 0;
-                  ++n_tile[s];
-                  if (++cj[s] == cnt[s]) {
-                    cj[s] = 0;
-                    if (++cg[s] < sc.ngroups) cnt[s] = sc.ntiles(s, cg[s]);
+                ++n_pv;
+                if (cj == cnt - 1) tc_commit(&bars->kv_empty[stage]);  // last tile of this stream on the slot
+                if (++kp == nkv) {  // tile finished: next tile / next group
+                  ks = kp = 0;
+                  ++n_tile;
+                  if (++cj == cnt) {
+                    cj = 0;
+                    if (++cg < sc.ngroups) cnt = sc.ntiles(s, cg);
                   }
                 }
               }
             }
           }
-          if (!progress) __nanosleep(kPollSleepNs);
+          
         }
       }
     }
