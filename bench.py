@@ -44,7 +44,7 @@ MOE_EXPERTS = {"cfg5_moe_5x_clip_b32_llama8b": 5}
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` capture of this command at
 # cfg2 B=256 (profiles/r01h_ncu_full_summary.txt): GEMM = mean over one encoder layer's four launches
 # (fc2+stats 1.818, qkv(LN folded) 1.182, out-proj+stats 0.877, fc1(LN folded) 1.487 GB).
-NCU_TRAFFIC = {"cfg2_clip_l14_336_llama8b": {"gemm": 1.341e9, "attention": 1.1849e9, "layernorm": 0.5464e9}}
+NCU_TRAFFIC = {"cfg2_clip_l14_336_llama8b": {"gemm": 1.386e9, "attention": 1.1849e9, "layernorm": 0.5464e9}}
 
 
 def workload(wl):
@@ -356,12 +356,12 @@ def run_b200(args):
                               "(mm_preprocess_images, bit-exact vs the HF processor) instead of on the CPU"},
         "gpu_launches": launches_per_step * args.steps,
         "gpu_launches_per_step": launches_per_step,
-        "roofline": {"kernel": "gemm_bf16_tn_kernel<false> (tcgen05 GEMM, %d launches/step)" % (n_gemm // max(1, args.steps)),
+        "roofline": {"kernel": "gemm_bf16_tn_kernel<false,ACT,LN,pair> (tcgen05 cta_group::2 GEMM, %d launches/step)" % (n_gemm // max(1, args.steps)),
                      "bound": "tensor", "achieved": gemm_tf, "peak": pk["tf_sust"], "unit": "TFLOP/s",
                      "frac": gemm_tf / pk["tf_sust"],
                      "traffic": NCU_TRAFFIC.get(args.workload, {}).get("gemm") if images == w["images"] else None,
                      "traffic_src": "ncu --set full, mean bytes per launch over one encoder layer's 4 GEMMs "
-                                    "(profiles/r01h_ncu_full_summary.txt)",
+                                    "(profiles/r01k_ncu_full_summary.txt)",
                      "peak_kind": f"{pk['src']} sustained cuBLAS bf16 (kernel timed inside a long step)",
                      "frac_of_burst": gemm_tf / pk["tf_burst"]},
         "path_tensor": {"achieved": path_tf, "unit": "TFLOP/s", "frac_of_sustained": path_tf / pk["tf_sust"],
