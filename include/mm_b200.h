@@ -192,6 +192,21 @@ int mm_patch_embed(const void* pixels, int pixel_dtype, int64_t B, int64_t img, 
                    const void* cls, void* out, int64_t D, void* stream);
 
 /*
+ * mm_patch_embed_ws — the same operator in two passes (the faster one; same inputs, outputs and rounding points):
+ *   1. patch rows: pixels -> bf16 [B*P, Kpad] (k = (c, ky, kx), zero padded), each pixel read once from HBM;
+ *   2. the TMA-fed CTA-pair GEMM (mm_gemm_bias_act's kernel) with the position-embedding / CLS-offset epilogue.
+ * The in-kernel gather of mm_patch_embed re-reads every patch once per 256 output columns through 4-byte loads and
+ * runs 8x slower at cfg2 shapes; it is kept for callers that cannot provide scratch memory.
+ *   workspace: device scratch of at least mm_patch_embed_workspace_bytes(B, img, patch) bytes, 16-byte aligned
+ *   (contents undefined afterwards).  Results are bit-identical to mm_patch_embed.
+ */
+int64_t mm_patch_embed_workspace_bytes(int64_t B, int64_t img, int64_t patch);
+int mm_patch_embed_ws(const void* pixels, int pixel_dtype, int64_t B, int64_t img, int64_t patch,
+                      const void* weight, int64_t ldw, const void* conv_bias, const void* pos_emb,
+                      const void* cls, void* out, int64_t D, void* workspace, int64_t workspace_bytes,
+                      void* stream);
+
+/*
  * mm_attention_fwd — non-causal softmax(Q·Kᵀ·scale)·V for every (image, head), no mask,
  * tcgen05 QKᵀ / PV with TMEM accumulators and an online softmax in registers.
  * Replaces HF:models/clip/modeling_clip.py:318-331 and HF:models/siglip/modeling_siglip.py:285-300

@@ -36,6 +36,8 @@ SIGNATURES = {
     "mm_set_gemm_pair": (None, [i32]),
     "mm_gemm_ln_bias_act": (i32, [vp, i64, vp, i64, vp, vp, i64, i64, i64, i64, i32, vp, i64, vp, i64, vp, vp, f32, vp]),
     "mm_patch_embed": (i32, [vp, i32, i64, i64, i64, vp, i64, vp, vp, vp, vp, i64, vp]),
+    "mm_patch_embed_workspace_bytes": (i64, [i64, i64, i64]),
+    "mm_patch_embed_ws": (i32, [vp, i32, i64, i64, i64, vp, i64, vp, vp, vp, vp, i64, vp, i64, vp]),
     "mm_attention_head_stride": (i64, [i64]),
     "mm_attention_fwd": (i32, [vp, vp, i64, i64, i64, i64, f32, vp]),
     "mm_weighted_expert_sum": (i32, [vp, vp, vp, vp, i64, i64, i64, i64, vp]),

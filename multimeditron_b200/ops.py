@@ -304,9 +304,13 @@ def fold_layernorm(w: torch.Tensor, bias: torch.Tensor | None, gamma: torch.Tens
     return q.contiguous(), b.to(torch.bfloat16).contiguous()
 
 
+_patch_ws: dict = {}   # device -> scratch for the staged patch rows (grown on demand, reused across calls)
+
+
 def patch_embed(pixels: torch.Tensor, weight_padded: torch.Tensor, conv_bias, pos_emb: torch.Tensor, cls,
-                patch: int, out: torch.Tensor | None = None) -> torch.Tensor:
-    """pixels [B,3,img,img] fp32/bf16; weight_padded [D, Kpad] bf16 (zero padded) -> [B,T,D] bf16."""
+                patch: int, out: torch.Tensor | None = None, staged: bool = True) -> torch.Tensor:
+    """pixels [B,3,img,img] fp32/bf16; weight_padded [D, Kpad] bf16 (zero padded) -> [B,T,D] bf16.
+    staged=True: patch rows -> bf16 scratch -> CTA-pair GEMM (mm_patch_embed_ws); False: in-kernel gather."""
     _cuda(pixels, weight_padded, conv_bias, pos_emb, cls)
     lib = _lib.load()
     B, Cc, img, img2 = pixels.shape
@@ -316,8 +320,20 @@ def patch_embed(pixels: torch.Tensor, weight_padded: torch.Tensor, conv_bias, po
     if out is None:
         out = torch.empty(B, T, D, dtype=torch.bfloat16, device=pixels.device)
     with _timed("mm_patch_embed", 2.0 * B * (T - (1 if cls is not None else 0)) * D * 3 * patch * patch):
-        rc = lib.mm_patch_embed(_ptr(pixels), _dt(pixels), B, img, patch, _ptr(weight_padded), weight_padded.stride(0),
-                            _ptr(conv_bias), _ptr(pos_emb), _ptr(cls), _ptr(out), D, _stream())
+        if staged and B > 0:
+            global LAUNCHES
+            LAUNCHES += 1   # patch_rows_kernel (the context manager counts the GEMM and the CLS kernel)
+            need = int(lib.mm_patch_embed_workspace_bytes(B, img, patch))
+            ws = _patch_ws.get(pixels.device)
+            if ws is None or ws.numel() < need:
+                ws = _patch_ws[pixels.device] = torch.empty(need, dtype=torch.uint8, device=pixels.device)
+            rc = lib.mm_patch_embed_ws(_ptr(pixels), _dt(pixels), B, img, patch, _ptr(weight_padded),
+                                       weight_padded.stride(0), _ptr(conv_bias), _ptr(pos_emb), _ptr(cls), _ptr(out), D,
+                                       _ptr(ws), ws.numel(), _stream())
+        else:
+            rc = lib.mm_patch_embed(_ptr(pixels), _dt(pixels), B, img, patch, _ptr(weight_padded),
+                                    weight_padded.stride(0), _ptr(conv_bias), _ptr(pos_emb), _ptr(cls), _ptr(out), D,
+                                    _stream())
     _check(rc, "mm_patch_embed")
     return out
 

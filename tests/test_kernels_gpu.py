@@ -193,6 +193,7 @@ def test_gemm_rejects_bad_arguments():
     (2, 56, 14, 256, False, True, torch.bfloat16),     # SigLIP-style: conv bias, no CLS, bf16 pixels
     (2, 384, 14, 1152, False, True, torch.float32),    # SigLIP so400m: 384 % 14 != 0, the conv drops the last 6 pixels
     (3, 61, 14, 128, True, False, torch.bfloat16),     # odd image size, remainder 5
+    (9, 336, 14, 1024, True, False, torch.float32),    # many row tiles: persistent pairs, modular position rows
 ])
 def test_patch_embed(B, img, p, D, cls, bias, dt):
     G = img // p
@@ -206,7 +207,9 @@ def test_patch_embed(B, img, p, D, cls, bias, dt):
     K = 3 * p * p
     wp = torch.zeros(D, (K + 63) // 64 * 64, device=DEV).bfloat16()
     wp[:, :K] = w.reshape(D, -1)
-    out = ops.patch_embed(px, wp, bs, pos, c, p)
+    out = ops.patch_embed(px, wp, bs, pos, c, p)                       # staged patch rows + CTA-pair GEMM
+    out_gather = ops.patch_embed(px, wp, bs, pos, c, p, staged=False)  # in-kernel gather (mm_patch_embed)
+    assert torch.equal(out, out_gather)                                # same operands, same k order: bit-identical
     ref = F.conv2d(px.bfloat16().float(), w.float(), bs.float() if bias else None, stride=p).flatten(2).transpose(1, 2)
     if cls:
         ref = torch.cat([c.float().expand(B, 1, D), ref], 1)
