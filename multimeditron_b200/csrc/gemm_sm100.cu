@@ -320,21 +320,6 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA, kPair>::kThreads, 1)
     if (fold_mode) load_stats(tile0);
     for (int t = tile0; t < num_tiles; t += tile_step) {
       const int m0 = (t / p.tiles_n) * kTileRows + m_off, n0 = (t % p.tiles_n) * BN;
-      // residual rows of the NEXT tile -> L2, a whole tile ahead: the epilogue's residual loads are otherwise full DRAM
-      // round trips (two per tile, in series), which a K = 1024 main loop cannot hide (out-proj: 80 % tensor-active)
-      if (!kGatherA && (LN == 0 || LN == 1) && p.residual != nullptr) {
-        const int tn = t + tile_step;
-        if (tn < num_tiles) {
-          const int e = (int)threadIdx.x - 128;   // 0..255: row = e / 2, 256-byte half = e % 2
-          const int pm = (tn / p.tiles_n) * kTileRows + m_off + (e >> 1);
-          const int pc = (tn % p.tiles_n) * BN + (e & 1) * 128;
-          if (pm < p.M && pc < p.N) {
-            const __nv_bfloat16* a = p.residual + (int64_t)(pm + p.res_row_off) * p.ldr + pc;
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
-            if (pc + 64 < p.N) asm volatile("prefetch.global.L2 [%0];" ::"l"(a + 64));
-          }
-        }
-      }
       // destination row of this lane's GEMM row
       const int my_m = m0 + q * 32 + lane;
       int my_out = -1;
