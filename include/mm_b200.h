@@ -108,6 +108,19 @@ int mm_embed_splice_fused(void* out, int64_t n_pos, int64_t hidden, int dst_dtyp
 int mm_embed_gather(void* out, int64_t n_pos, int64_t hidden, int dtype, const void* table,
                     int64_t vocab, const int64_t* input_ids, int32_t* status, void* stream);
 
+/* mm_embed_gather_skip — mm_embed_gather that leaves rows with input_ids[r] == skip_id untouched: the caller's
+ * splice (mm_splice_scatter or the projector GEMM's scatter epilogue) writes every attachment position, so the
+ * attachment token's own embedding row (model.py:433) is never observable and need not be copied. */
+int mm_embed_gather_skip(void* out, int64_t n_pos, int64_t hidden, int dtype, const void* table,
+                         int64_t vocab, const int64_t* input_ids, int64_t skip_id, int32_t* status,
+                         void* stream);
+
+/* mm_gather_rows — out[k,:] = src[rows[k],:]  (k < n_rows; rows int32, bounds-checked against n_src_rows ->
+ * MM_STATUS_INDEX_OOB).  The backward of the splice statement model.py:441-444: the gradient of the projected
+ * tokens is the gradient of inputs_embeds at their positions. */
+int mm_gather_rows(void* out, int64_t n_rows, int64_t hidden, int dst_dtype, const void* src,
+                   int64_t n_src_rows, int src_dtype, const int32_t* rows, int32_t* status, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * ViT / projector building blocks (bf16 storage, fp32 accumulate)
  * ------------------------------------------------------------------------------------------ */
@@ -161,6 +174,17 @@ int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, con
  * LN itself stays in fp32 — same error scale (2^-9 relative per operand), covered by the stated bf16 tolerance.
  */
 int64_t mm_gemm_row_stats_slots(int64_t N);
+
+/*
+ * mm_fold_layernorm — load-time weight preparation for the consumer side of mm_gemm_ln_bias_act (no reference
+ * counterpart: the reference keeps nn.LayerNorm as its own kernel, HF:models/clip/modeling_clip.py:371,380).
+ *   W_out[n,k] = bf16 of gamma[k]*W[n,k] - mean_k(gamma*W[n,:]), rounded with error feedback along k (the bf16 row
+ *                sums stay within half an ulp of zero, so the LayerNorm mean term cancels inside the MMA)
+ *   bias_out[n] = bf16(bias[n] + sum_k beta[k]*W[n,k])      (bias may be NULL)
+ * W [N, K] bf16 row-major (ldw elements per row), gamma/beta [K] bf16.  One thread per row; K <= 12000.
+ */
+int mm_fold_layernorm(const void* W, int64_t ldw, const void* bias, const void* gamma, const void* beta,
+                      void* W_out, int64_t ldo, void* bias_out, int64_t N, int64_t K, void* stream);
 
 /*
  * mm_set_gemm_pair — tuning switch of mm_gemm_bias_act / mm_gemm_ln_bias_act (no reference counterpart).
@@ -271,6 +295,26 @@ int64_t mm_preprocess_workspace_bytes(int64_t B, int64_t S, int64_t kmax);
 int mm_preprocess_images(const void* src, const int64_t* desc, int64_t B, int64_t S, int64_t kmax,
                          int64_t max_h, int64_t max_w, void* ws, void* tmp, const float* mean255,
                          const float* std255, void* out, int out_dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Projector training step (reference: freeze_for_alignment, model.py:310-326,
+ * MLPProjector projectors/mlp.py:33-39 under torch.autograd).  The backward GEMMs are mm_gemm_bias_act calls on
+ * transposed operands:  dX = dY·W  ->  A = dY [M,N], "W" = Wᵀ [K,N];   dW = dYᵀ·X -> A = dYᵀ [N,M], "W" = Xᵀ [K,M].
+ * ------------------------------------------------------------------------------------------ */
+
+/* a = GELU_erf(z), element-wise bf16 (n % 8 == 0); bit-identical to the fused MM_ACT_GELU_ERF epilogue. */
+int mm_gelu_fwd(const void* z, void* a, int64_t n, void* stream);
+
+/* bytes of fp32 scratch mm_gelu_bwd_colsum needs for an [M, N] operand */
+int64_t mm_colsum_workspace_bytes(int64_t M, int64_t N);
+
+/* dz = da * GELU_erf'(z) (bf16 [M,N], fp32 math, one rounding) and bias_grad[n] = sum_m dz[m,n] (fp32 [N],
+ * deterministic two-stage sum over the bf16 values as stored).  z == dz == NULL: column sum of `da` only. */
+int mm_gelu_bwd_colsum(const void* da, const void* z, void* dz, float* bias_grad, void* workspace, int64_t M,
+                       int64_t N, void* stream);
+
+/* out [C, R] = in [R, C]ᵀ, bf16, R % 8 == C % 8 == 0. */
+int mm_transpose(const void* in, void* out, int64_t R, int64_t C, void* stream);
 
 #ifdef __cplusplus
 }

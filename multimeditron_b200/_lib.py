@@ -30,10 +30,17 @@ SIGNATURES = {
     "mm_splice_scatter_idx": (i32, [vp, i64, i64, i64, i32, vp, i64, i32, vp, vp, vp, vp]),
     "mm_embed_splice_fused": (i32, [vp, i64, i64, i32, vp, i64, vp, vp, vp, i64, i32, vp, vp]),
     "mm_embed_gather": (i32, [vp, i64, i64, i32, vp, i64, vp, vp, vp]),
+    "mm_embed_gather_skip": (i32, [vp, i64, i64, i32, vp, i64, vp, i64, vp, vp]),
+    "mm_gather_rows": (i32, [vp, i64, i64, i32, vp, i64, i32, vp, vp, vp]),
+    "mm_gelu_fwd": (i32, [vp, vp, i64, vp]),
+    "mm_colsum_workspace_bytes": (i64, [i64, i64]),
+    "mm_gelu_bwd_colsum": (i32, [vp, vp, vp, vp, vp, i64, i64, vp]),
+    "mm_transpose": (i32, [vp, vp, i64, i64, vp]),
     "mm_layernorm": (i32, [vp, vp, vp, vp, i64, i64, f32, i64, i64, i64, vp]),
     "mm_gemm_bias_act": (i32, [vp, i64, vp, i64, vp, vp, i64, i64, i64, i64, i32, vp, i64, i64, i64, vp, i64, vp]),
     "mm_gemm_row_stats_slots": (i64, [i64]),
     "mm_set_gemm_pair": (None, [i32]),
+    "mm_fold_layernorm": (i32, [vp, i64, vp, vp, vp, vp, i64, vp, i64, i64, vp]),
     "mm_gemm_ln_bias_act": (i32, [vp, i64, vp, i64, vp, vp, i64, i64, i64, i64, i32, vp, i64, vp, i64, vp, vp, f32, vp]),
     "mm_patch_embed": (i32, [vp, i32, i64, i64, i64, vp, i64, vp, vp, vp, vp, i64, vp]),
     "mm_patch_embed_workspace_bytes": (i64, [i64, i64, i64]),

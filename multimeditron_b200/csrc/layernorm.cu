@@ -107,3 +107,64 @@ extern "C" int mm_layernorm(const void* x, void* y, const void* gamma, const voi
   MM_CUDA_CHECK(cudaGetLastError());
   return MM_OK;
 }
+
+// ---- mm_fold_layernorm: weight preparation for the LayerNorm fold of mm_gemm_ln_bias_act (load time) --------------
+// One thread per weight row n (rows are independent; the error feedback is serial along k):
+//   wg[k]  = W[n,k]*gamma[k] - mean_k(W[n,:]*gamma)          (zero row sum: the LN mean term cancels inside the MMA)
+//   t      = wg[k] + err;  q = bf16(t);  err = t - q         (sigma-delta rounding: the bf16 row sum stays < 1/2 ulp)
+//   b'[n]  = bias[n] + sum_k W[n,k]*beta[k]
+// Row means and the beta dot product are accumulated in double (load-time kernel, accuracy over speed).
+namespace mm {
+__global__ void __launch_bounds__(128) fold_layernorm_kernel(const __nv_bfloat16* __restrict__ W, int64_t ldw,
+                                                             const __nv_bfloat16* __restrict__ bias,
+                                                             const __nv_bfloat16* __restrict__ gamma,
+                                                             const __nv_bfloat16* __restrict__ beta,
+                                                             __nv_bfloat16* __restrict__ Wout, int64_t ldo,
+                                                             __nv_bfloat16* __restrict__ bout, int N, int K) {
+  extern __shared__ float s_gb[];   // gamma[K] | beta[K]
+  for (int k = threadIdx.x; k < K; k += blockDim.x) {
+    s_gb[k] = __bfloat162float(gamma[k]);
+    s_gb[K + k] = __bfloat162float(beta[k]);
+  }
+  __syncthreads();
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const __nv_bfloat16* w = W + (int64_t)n * ldw;
+  double sum = 0.0, dot = 0.0;
+  for (int k = 0; k < K; ++k) {
+    const float x = __bfloat162float(w[k]);
+    sum += (double)(x * s_gb[k]);
+    dot += (double)x * (double)s_gb[K + k];
+  }
+  const float mean = (float)(sum / (double)K);
+  float err = 0.f;
+  __nv_bfloat16* o = Wout + (int64_t)n * ldo;
+  for (int k = 0; k < K; ++k) {
+    const float t = (__bfloat162float(w[k]) * s_gb[k] - mean) + err;
+    const __nv_bfloat16 q = __float2bfloat16_rn(t);
+    o[k] = q;
+    err = t - __bfloat162float(q);
+  }
+  bout[n] = __float2bfloat16_rn((float)(dot + (bias ? (double)__bfloat162float(bias[n]) : 0.0)));
+}
+}  // namespace mm
+
+extern "C" int mm_fold_layernorm(const void* W, int64_t ldw, const void* bias, const void* gamma, const void* beta,
+                                 void* W_out, int64_t ldo, void* bias_out, int64_t N, int64_t K, void* stream) {
+  using namespace mm;
+  if (N < 0 || K <= 0 || K > 12000 || ldw < K || ldo < K || N > INT32_MAX / 2) return MM_ERR_BAD_ARG;
+  if (N == 0) return MM_OK;
+  if (!W || !gamma || !beta || !W_out || !bias_out) return MM_ERR_BAD_ARG;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int threads = 128;
+  const int grid = (int)((N + threads - 1) / threads);
+  const size_t smem = 2 * (size_t)K * sizeof(float);
+  if (smem > 48 * 1024)
+    MM_CUDA_CHECK(cudaFuncSetAttribute(fold_layernorm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  fold_layernorm_kernel<<<grid, threads, smem, st>>>(
+      reinterpret_cast<const __nv_bfloat16*>(W), ldw, reinterpret_cast<const __nv_bfloat16*>(bias),
+      reinterpret_cast<const __nv_bfloat16*>(gamma), reinterpret_cast<const __nv_bfloat16*>(beta),
+      reinterpret_cast<__nv_bfloat16*>(W_out), ldo, reinterpret_cast<__nv_bfloat16*>(bias_out), (int)N, (int)K);
+  MM_CUDA_CHECK(cudaGetLastError());
+  return MM_OK;
+}

@@ -194,7 +194,8 @@ constexpr int kMoveUnroll = 8;
 // mode 0: scatter  dest[rows[k]] = src[k]          (k over n_rows)
 // mode 1: scatter with (batch_idx, token_range) int64 pairs
 // mode 2: fused    out[r] = sop[r]>=0 ? src[sop[r]] : table[ids[r]]   (r over n_pos)
-// mode 3: gather   out[r] = table[ids[r]]
+// mode 3: gather   out[r] = table[ids[r]]   (rows with ids[r] == skip_id are left untouched: the splice overwrites them)
+// mode 4: gather   out[k] = src[rows[k]]     (backward of the splice: gradient rows of the projected tokens)
 struct MoveArgs {
   void* dest;
   const void* src;
@@ -209,6 +210,7 @@ struct MoveArgs {
   int64_t n_dest_rows; // bound for scatter destinations
   int64_t n_src_rows;  // bound for src rows (fused)
   int64_t batch, seq, vocab, hidden;
+  int64_t skip_id;     // mode 3: id whose rows are not written (-1: none)
 };
 
 template <int MODE, typename S, typename D>
@@ -222,6 +224,15 @@ __device__ __forceinline__ bool resolve(const MoveArgs& a, int64_t u, const S*& 
     }
     sp = reinterpret_cast<const S*>(a.src) + u * H;
     dp = reinterpret_cast<D*>(a.dest) + r * H;
+    return true;
+  } else if (MODE == 4) {
+    int64_t r = a.rows[u];
+    if (r < 0 || r >= a.n_src_rows) {
+      if (a.status) atomicOr(a.status, MM_STATUS_INDEX_OOB);
+      return false;
+    }
+    sp = reinterpret_cast<const S*>(a.src) + r * H;
+    dp = reinterpret_cast<D*>(a.dest) + u * H;
     return true;
   } else if (MODE == 1) {
     int64_t b = a.bidx[u], t = a.trange[u];
@@ -269,12 +280,14 @@ __global__ void __launch_bounds__(kMoveThreads) move_rows_kernel(MoveArgs a) {
     const D* tp = nullptr;
     if (resolve<MODE, S, D>(a, u, sp, dp)) {
       kind = 1;
-    } else if (MODE >= 2) {
+    } else if (MODE == 2 || MODE == 3) {
       const bool is_src = (MODE == 2) && (a.sop[u] >= 0);
       if (!is_src) {
         const int64_t id = a.ids[u];
         if (id < 0 || id >= a.vocab) {
           if (a.status && lane == 0) atomicOr(a.status, MM_STATUS_INDEX_OOB);
+        } else if (MODE == 3 && id == a.skip_id) {
+          // attachment position: the splice writes this row
         } else {
           kind = 2;
           tp = reinterpret_cast<const D*>(a.table) + id * a.hidden;
@@ -316,12 +329,13 @@ __global__ void __launch_bounds__(kMoveThreads) move_rows_scalar_kernel(MoveArgs
     D* dp = nullptr;
     if (resolve<MODE, S, D>(a, u, sp, dp)) {
       dp[c] = cvt1<S, D>(sp[c]);
-    } else if (MODE >= 2) {
+    } else if (MODE == 2 || MODE == 3) {
       bool is_src = (MODE == 2) && (a.sop[u] >= 0);
       int64_t id = a.ids[u];
       if (!is_src) {
         if (id < 0 || id >= a.vocab) {
           if (a.status) atomicOr(a.status, MM_STATUS_INDEX_OOB);
+        } else if (MODE == 3 && id == a.skip_id) {
         } else {
           dp[c] = reinterpret_cast<const D*>(a.table)[id * a.hidden + c];
         }
@@ -455,8 +469,8 @@ extern "C" int mm_embed_splice_fused(void* out, int64_t n_pos, int64_t hidden, i
   return dispatch_move<2>(a, src_dtype, dst_dtype, reinterpret_cast<cudaStream_t>(stream));
 }
 
-extern "C" int mm_embed_gather(void* out, int64_t n_pos, int64_t hidden, int dtype, const void* table,
-                               int64_t vocab, const int64_t* input_ids, int32_t* status, void* stream) {
+static int embed_gather_impl(void* out, int64_t n_pos, int64_t hidden, int dtype, const void* table, int64_t vocab,
+                             const int64_t* input_ids, int64_t skip_id, int32_t* status, void* stream) {
   if (n_pos < 0 || hidden < 0 || vocab < 0) return MM_ERR_BAD_ARG;
   if (n_pos > 0 && (!out || !table || !input_ids)) return MM_ERR_BAD_ARG;
   MoveArgs a{};
@@ -467,7 +481,35 @@ extern "C" int mm_embed_gather(void* out, int64_t n_pos, int64_t hidden, int dty
   a.n_units = n_pos;
   a.vocab = vocab;
   a.hidden = hidden;
+  a.skip_id = skip_id;
   return dispatch_move<3>(a, dtype, dtype, reinterpret_cast<cudaStream_t>(stream));
+}
+
+extern "C" int mm_embed_gather(void* out, int64_t n_pos, int64_t hidden, int dtype, const void* table,
+                               int64_t vocab, const int64_t* input_ids, int32_t* status, void* stream) {
+  return embed_gather_impl(out, n_pos, hidden, dtype, table, vocab, input_ids, -1, status, stream);
+}
+
+extern "C" int mm_embed_gather_skip(void* out, int64_t n_pos, int64_t hidden, int dtype, const void* table,
+                                    int64_t vocab, const int64_t* input_ids, int64_t skip_id, int32_t* status,
+                                    void* stream) {
+  return embed_gather_impl(out, n_pos, hidden, dtype, table, vocab, input_ids, skip_id, status, stream);
+}
+
+extern "C" int mm_gather_rows(void* out, int64_t n_rows, int64_t hidden, int dst_dtype, const void* src,
+                              int64_t n_src_rows, int src_dtype, const int32_t* rows, int32_t* status, void* stream) {
+  if (n_rows < 0 || hidden < 0 || n_src_rows < 0) return MM_ERR_BAD_ARG;
+  if (n_rows > 0 && (!out || !src || !rows)) return MM_ERR_BAD_ARG;
+  MoveArgs a{};
+  a.dest = out;
+  a.src = src;
+  a.rows = rows;
+  a.status = status;
+  a.n_units = n_rows;
+  a.n_src_rows = n_src_rows;
+  a.hidden = hidden;
+  a.skip_id = -1;
+  return dispatch_move<4>(a, src_dtype, dst_dtype, reinterpret_cast<cudaStream_t>(stream));
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -53,3 +53,33 @@ class H2DUploader:
         for slot in self.in_use:
             slot["free"] = ev
         self.in_use = []
+
+
+class HostStager:
+    """The collator hands a modality its inputs as a Python LIST of per-image CPU tensors (data_loader.py:126,131,
+    144-152); the reference stacks them into pageable memory and copies synchronously (image_modality.py:131-132).
+    Here the list is stacked straight into one of `depth` cached PINNED staging buffers (one host memcpy per image, no
+    intermediate tensor) and uploaded on the copy stream; a staging buffer is reused only after its own H2D finished
+    (event), so with depth 2 the host never waits for the copy it issued one step earlier."""
+
+    def __init__(self, device, uploader: "H2DUploader | None" = None, depth: int = 2):
+        self.device = torch.device(device)
+        self.uploader = uploader or H2DUploader(device)
+        self.slots = [dict(buf=None, done=None) for _ in range(depth)]
+        self.i = 0
+
+    def stack_upload(self, inputs) -> torch.Tensor:
+        """list of equally-shaped CPU tensors -> [B, ...] on the device, valid on the current stream."""
+        shape, dt = (len(inputs), *inputs[0].shape), inputs[0].dtype
+        slot = self.slots[self.i]
+        self.i = (self.i + 1) % len(self.slots)
+        buf = slot["buf"]
+        if buf is None or buf.shape != shape or buf.dtype != dt:
+            buf = slot["buf"] = torch.empty(shape, dtype=dt, pin_memory=True)
+            slot["done"] = None
+        if slot["done"] is not None:
+            slot["done"].synchronize()      # the H2D issued `depth` steps ago out of this buffer
+        torch.stack(inputs, dim=0, out=buf)
+        out = self.uploader.upload(buf)
+        slot["done"] = self.uploader.last_ready
+        return out

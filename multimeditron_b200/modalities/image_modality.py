@@ -13,7 +13,7 @@ from typing import Any, Dict, List, Optional
 import torch
 
 from ..configs import TOWERS, TowerConfig
-from ..h2d import H2DUploader
+from ..h2d import H2DUploader, HostStager
 from ..preprocess import DevicePreprocessor, PackedImages
 from ..vit import ProjectorWeights, TowerRunner, TowerWeights
 from .base import AutoModality, BaseModality, BaseModalityConfig, BaseModalityProcessor
@@ -97,11 +97,11 @@ class B200ImageModality(BaseModality):
         self.embedding_size = self.tower.hidden_size
         self._num_patches_per_entry = self.tower.num_patches
         self._runner: Optional[TowerRunner] = None
-        self._staging: Optional[torch.Tensor] = None
-        self._staging_event = None
+        self._stager: Optional[HostStager] = None
         self._pre: Optional[DevicePreprocessor] = None
         self._up: Optional[H2DUploader] = None
         self._frozen = True
+        self.projector: Optional[torch.nn.Module] = None
         if state_dict is not None:
             self.load_reference_state_dict(state_dict, device or torch.device("cuda", torch.cuda.current_device()))
 
@@ -153,29 +153,35 @@ class B200ImageModality(BaseModality):
             return self._preprocessor()(inputs, dev, torch.bfloat16)
         if len(inputs) and inputs[0].is_cuda:
             return torch.stack(inputs, dim=0)
-        # one cached pinned staging buffer + one async H2D instead of the reference's pageable, synchronous
-        # copy (:131-132)
         if not inputs:
             return torch.empty(0, 3, self.tower.image_size, self.tower.image_size, device=dev)
-        shape, dt = (len(inputs), *inputs[0].shape), inputs[0].dtype
-        buf = self._staging
-        if buf is None or buf.shape != shape or buf.dtype != dt:
-            buf = self._staging = torch.empty(shape, dtype=dt, pin_memory=True)
-        if self._staging_event is not None:
-            self._staging_event.synchronize()  # the previous H2D out of this buffer must have finished
-        torch.stack(inputs, dim=0, out=buf)
-        out = self._uploader().upload(buf)
-        self._staging_event = self._uploader().last_ready
-        return out
+        # the collator's format: a list of per-image CPU tensors -> pinned staging + one async H2D on the copy stream
+        # instead of the reference's pageable, synchronous copy (:131-132)
+        if self._stager is None:
+            self._stager = HostStager(dev, self._uploader())
+        return self._stager.stack_upload(inputs)
 
     def _release(self):
         if self._up is not None:
             self._up.release()
 
-    @torch.no_grad()
+    @property
+    def projector_trainable(self) -> bool:
+        return self.projector is not None and any(p.requires_grad for p in self.projector.parameters())
+
     def forward(self, inputs: List[torch.Tensor]) -> torch.Tensor:
-        y = self.runner.forward(self._stack(inputs))
-        self._release()
+        """image_modality.py:130-137.  Frozen / no-grad: kernels only.  Projector unfrozen and autograd on: the tower
+        runs on the kernels without a graph, the projector as autograd_ops.ProjectorFunction (forward + backward)."""
+        if torch.is_grad_enabled() and self.projector_trainable:
+            with torch.no_grad():
+                px = self._stack(inputs)
+                feats = self.runner.features(px).clone()
+                self._release()
+            from ..autograd_ops import projector_forward
+            return projector_forward(feats, self.projector).view(px.shape[0], self.tower.num_patches, -1)
+        with torch.no_grad():
+            y = self.runner.forward(self._stack(inputs))
+            self._release()
         return y
 
     @torch.no_grad()
@@ -186,12 +192,38 @@ class B200ImageModality(BaseModality):
         self._release()
         return y
 
-    # -- training-mode switches (interface parity; backward is not part of this round) ------------------------------
+    # -- training-mode switches (base.py:120-143) ---------------------------------------------------------------
     def freeze_modality_embedder(self):
         self._frozen = True
 
     def unfreeze_modality_embedder(self):
-        raise NotImplementedError("ViT backward on the B200 path is SURVEY.md §8(f)#2 (next)")
+        raise NotImplementedError("ViT backward on the B200 path is not built (SURVEY.md §8(f)#2 lists it as optional); "
+                                  "the reference's ALIGNMENT stage (projector only) is supported: unfreeze_projection()")
 
     def unfreeze_projection(self):
-        raise NotImplementedError("projector backward on the B200 path is SURVEY.md §8(f)#2 (next)")
+        """model.py:310-326 (freeze_for_alignment): expose the projector as nn.Parameters
+        (`projector.projection.{0,2,4}.{weight,bias}` — the reference's state-dict keys) that SHARE storage with the
+        kernel-side weights, so an optimizer's in-place updates are what the next forward multiplies by."""
+        if self.projector is None:
+            self.projector = _ProjectorParams(self.runner.w.proj)
+        for p in self.projector.parameters():
+            p.requires_grad = True
+
+    def freeze_projection(self):
+        if self.projector is not None:
+            for p in self.projector.parameters():
+                p.requires_grad = False
+
+
+class _ProjectorParams(torch.nn.Module):
+    """nn.Parameter view of ProjectorWeights (bf16, same storage), laid out like MLPProjector (projectors/mlp.py:33-39)."""
+
+    def __init__(self, pw: ProjectorWeights):
+        super().__init__()
+        layers = []
+        for w, b in ((pw.w0, pw.b0), (pw.w2, pw.b2), (pw.w4, pw.b4)):
+            lin = torch.nn.Linear(w.shape[1], w.shape[0], device="meta")
+            lin.weight = torch.nn.Parameter(w, requires_grad=False)
+            lin.bias = torch.nn.Parameter(b, requires_grad=False)
+            layers += [lin, torch.nn.GELU()]
+        self.projection = torch.nn.Sequential(*layers[:-1])

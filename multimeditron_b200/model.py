@@ -54,49 +54,92 @@ class B200MultiModalEmbedder(torch.nn.Module):
         return self._status
 
     def check(self):
-        """Lazy (one sync) check of data-dependent errors; raises IndexError / RuntimeError like the reference."""
+        """Lazy (one sync) check of data-dependent errors; raises IndexError / RuntimeError like the reference.
+        The status word is cleared whether or not the check raises, so one bad batch cannot poison later checks.
+        NOTE: for DEVICE-resident input_ids the result of `embed_modalities_with_text` is only valid once this
+        check has passed (rows may be missing after a count mismatch); host-resident ids are verified eagerly."""
         if self._status is not None:
-            ops.raise_for_status(self._status)
-            self._status.zero_()
+            try:
+                ops.raise_for_status(self._status)
+            finally:
+                self._status.zero_()
 
-    @torch.no_grad()
+    def _eager_host_checks(self, input_ids: torch.Tensor, stacks, positions_from: str):
+        """The collator hands over HOST ids: verify what the reference would trip over BEFORE launching anything
+        (same exception classes as nn.Embedding / index_put_, model.py:433,441) — no device round trip needed."""
+        V, H = self.embed_table.shape
+        if input_ids.numel() and (int(input_ids.min()) < 0 or int(input_ids.max()) >= V):
+            raise IndexError("index out of range in self")
+        if positions_from == "device":
+            have = int((input_ids == self.attachment_token_idx).sum())
+            want = 0
+            for name, stack in stacks.items():
+                m = self._get_modality_by_name(name)
+                want += len(stack) * getattr(m, "rows_per_entry", m._num_patches_per_entry)
+            if have != want:
+                raise RuntimeError(f"shape mismatch: value tensor of shape [{want}, {H}] cannot be broadcast to "
+                                   f"indexing result of shape [{have}, {H}]")
+
     def embed_modalities_with_text(self, input_ids: torch.Tensor, processed_multimodal_inputs: Dict[str, Any],
-                                   positions_from: str = "collator") -> torch.Tensor:
+                                   positions_from: str = "collator", eager_checks: bool = True) -> torch.Tensor:
         """model.py:410-446.  positions_from:
           'collator' — use processed_multimodal_inputs['batch_idx'/'token_range'] as the reference does;
           'device'   — ignore them and derive the positions from input_ids with the device prefix sum
-                       (valid for a single modality type); no index H2D at all."""
+                       (valid for a single modality type); no index H2D at all.
+        Autograd: runs without a graph unless a modality's projector is trainable (`unfreeze_projection()`), in which
+        case the projector and the splice are differentiable (autograd_ops); the embedding table is treated as frozen
+        and a table that requires grad raises instead of losing its gradient silently."""
         dev = self.embed_table.device
-        ids = input_ids.to(dev, non_blocking=True)
-        st = self.status()
         stacks = processed_multimodal_inputs["stacked"]
-        B, S = ids.shape
-        H = self.embed_table.shape[1]
         if positions_from == "device" and len(stacks) > 1:
             raise ValueError("device-side positions need a single modality type")
-        embedded = ops.embed_gather(self.embed_table, ids, status=st)                       # :433
+        if torch.is_grad_enabled() and self.embed_table.requires_grad:
+            raise NotImplementedError("the embedding table requires grad: the B200 splice path does not produce that "
+                                      "gradient (freeze the LLM, or run under torch.no_grad())")
+        if eager_checks and not input_ids.is_cuda:
+            self._eager_host_checks(input_ids, stacks, positions_from)
+        ids = input_ids.to(dev, non_blocking=True)
+        st = self.status()
+        B, S = ids.shape
+        H = self.embed_table.shape[1]
+        trains = {n: torch.is_grad_enabled() and getattr(self._get_modality_by_name(n), "projector_trainable", False)
+                  for n in stacks}
+        with torch.no_grad():
+            # device positions cover exactly the ids == attachment_id rows: those need no embedding copy (:433)
+            skip = self.attachment_token_idx if (positions_from == "device" and stacks) else None
+            embedded = ops.embed_gather(self.embed_table.detach(), ids, status=st, skip_id=skip)   # :433
         for name, stack in stacks.items():
             modality = self._get_modality_by_name(name)
-            if positions_from == "device":
-                n_rows = len(stack) * getattr(modality, "rows_per_entry", modality._num_patches_per_entry)
-                dest_rows, _, _ = ops.attach_positions(ids, self.attachment_token_idx, expected_rows=n_rows,
-                                                       want_src_of_pos=False, status=st)
-            else:
-                bi = processed_multimodal_inputs["batch_idx"][name].to(dev, non_blocking=True)
-                tr = processed_multimodal_inputs["token_range"][name].to(dev, non_blocking=True)
-                dest_rows = None
-            fused = (self.fuse_splice and hasattr(modality, "forward_into") and embedded.dtype == torch.bfloat16)
+            with torch.no_grad():
+                if positions_from == "device":
+                    n_rows = len(stack) * getattr(modality, "rows_per_entry", modality._num_patches_per_entry)
+                    dest_rows, _, _ = ops.attach_positions(ids, self.attachment_token_idx, expected_rows=n_rows,
+                                                           want_src_of_pos=False, status=st)
+                else:
+                    bi = processed_multimodal_inputs["batch_idx"][name].to(dev, non_blocking=True)
+                    tr = processed_multimodal_inputs["token_range"][name].to(dev, non_blocking=True)
+                    dest_rows = None
+            fused = (self.fuse_splice and hasattr(modality, "forward_into") and embedded.dtype == torch.bfloat16
+                     and not trains[name])
             if fused and dest_rows is not None:
                 modality.forward_into(stack, embedded, dest_rows)                         # :439 + :441-444 fused
                 continue
             proj = modality(stack)                                                        # :439
-            proj2d = proj.reshape(-1, proj.shape[-1])
-            if dest_rows is not None:
+            proj2d = proj.reshape(-1, proj.shape[-1]).to(embedded.dtype)
+            if proj.requires_grad:
+                from .autograd_ops import splice_rows
+                rows = dest_rows if dest_rows is not None else (bi * S + tr).to(torch.int32)
+                if proj2d.shape[0] != rows.numel():
+                    raise RuntimeError("shape mismatch: number of modality embeddings != attachment positions")
+                embedded = splice_rows(embedded.view(B * S, H), proj2d, rows, st).view(B, S, H)
+            elif dest_rows is not None:
                 if proj2d.shape[0] != dest_rows.numel():
                     raise RuntimeError("shape mismatch: number of modality embeddings != attachment positions")
-                ops.splice_scatter(embedded.view(B * S, H), proj2d.contiguous(), dest_rows, status=st)
+                with torch.no_grad():
+                    ops.splice_scatter(embedded.view(B * S, H), proj2d.contiguous(), dest_rows, status=st)
             else:
-                ops.splice_scatter_idx(embedded, proj2d.contiguous(), bi, tr, status=st)  # :441-444
+                with torch.no_grad():
+                    ops.splice_scatter_idx(embedded, proj2d.contiguous(), bi, tr, status=st)  # :441-444
         return embedded
 
     @torch.no_grad()

@@ -165,16 +165,39 @@ def splice_scatter_idx(dest: torch.Tensor, src: torch.Tensor, batch_idx: torch.T
     return dest
 
 
-def embed_gather(table: torch.Tensor, input_ids: torch.Tensor, status: torch.Tensor | None = None) -> torch.Tensor:
+def embed_gather(table: torch.Tensor, input_ids: torch.Tensor, status: torch.Tensor | None = None,
+                 skip_id: int | None = None) -> torch.Tensor:
+    """table[input_ids] (model.py:433).  skip_id: rows whose id equals it are NOT written — for callers that splice
+    every attachment position afterwards (the rows of `out` at those positions are uninitialised until then)."""
     _cuda(table, input_ids)
     lib = _lib.load()
     V, H = table.shape
     ids = input_ids.contiguous()
     out = torch.empty(*ids.shape, H, dtype=table.dtype, device=table.device)
-    with _timed("mm_embed_gather", 2.0 * ids.numel() * H * table.element_size()):
-        rc = lib.mm_embed_gather(_ptr(out), ids.numel(), H, _dt(table), _ptr(table.contiguous()), V, _ptr(ids),
-                             _ptr(status), _stream())
+    n_copy = ids.numel()
+    with _timed("mm_embed_gather", 2.0 * n_copy * H * table.element_size()):
+        if skip_id is None:
+            rc = lib.mm_embed_gather(_ptr(out), ids.numel(), H, _dt(table), _ptr(table.contiguous()), V, _ptr(ids),
+                                     _ptr(status), _stream())
+        else:
+            rc = lib.mm_embed_gather_skip(_ptr(out), ids.numel(), H, _dt(table), _ptr(table.contiguous()), V, _ptr(ids),
+                                          int(skip_id), _ptr(status), _stream())
     _check(rc, "mm_embed_gather")
+    return out
+
+
+def gather_rows(src: torch.Tensor, rows: torch.Tensor, out_dtype=None, status: torch.Tensor | None = None) -> torch.Tensor:
+    """out[k] = src.view(-1,H)[rows[k]]  (rows int32) — the splice's backward (gradient of the projected tokens)."""
+    _cuda(src, rows)
+    lib = _lib.load()
+    H = src.shape[-1]
+    s2 = src.contiguous().view(-1, H)
+    assert rows.dtype == torch.int32 and rows.is_contiguous()
+    out = torch.empty(rows.numel(), H, dtype=out_dtype or src.dtype, device=src.device)
+    with _timed("mm_gather_rows", 2.0 * rows.numel() * H * src.element_size()):
+        rc = lib.mm_gather_rows(_ptr(out), rows.numel(), H, _dt(out), _ptr(s2), s2.shape[0], _dt(s2), _ptr(rows),
+                                _ptr(status), _stream())
+    _check(rc, "mm_gather_rows")
     return out
 
 
@@ -284,24 +307,22 @@ def row_stats_slots(n: int) -> int:
 
 
 def fold_layernorm(w: torch.Tensor, bias: torch.Tensor | None, gamma: torch.Tensor, beta: torch.Tensor):
-    """(W'', b') for the consumer side of mm_gemm_ln_bias_act.
+    """(W'', b') for the consumer side of mm_gemm_ln_bias_act — one launch of mm_fold_layernorm (load time).
     W'' = gamma*W with each row re-centred to zero sum, rounded to bf16 with error feedback along k (sigma-delta), so
     the bf16 row sums stay within half an ulp of zero and the LayerNorm mean term cancels inside the MMA;
     b' = bias + W @ beta, rounded to bf16."""
-    wf = w.float()
-    wg = wf * gamma.float()[None, :]
-    wg = wg - wg.mean(1, keepdim=True)
-    q = torch.empty_like(wg, dtype=torch.bfloat16)
-    err = torch.zeros(wg.shape[0], dtype=torch.float32, device=wg.device)
-    for k in range(wg.shape[1]):          # load-time only
-        t = wg[:, k] + err
-        qk = t.to(torch.bfloat16)
-        q[:, k] = qk
-        err = t - qk.float()
-    b = wf @ beta.float()
-    if bias is not None:
-        b = b + bias.float()
-    return q.contiguous(), b.to(torch.bfloat16).contiguous()
+    _cuda(w, bias, gamma, beta)
+    lib = _lib.load()
+    assert w.dtype == torch.bfloat16 and w.dim() == 2 and w.stride(1) == 1
+    N, K = w.shape
+    g, b = gamma.to(torch.bfloat16).contiguous(), beta.to(torch.bfloat16).contiguous()
+    bi = bias.to(torch.bfloat16).contiguous() if bias is not None else None
+    q = torch.empty(N, K, dtype=torch.bfloat16, device=w.device)
+    bo = torch.empty(N, dtype=torch.bfloat16, device=w.device)
+    with _timed("mm_fold_layernorm", 4.0 * N * K):
+        rc = lib.mm_fold_layernorm(_ptr(w), w.stride(0), _ptr(bi), _ptr(g), _ptr(b), _ptr(q), K, _ptr(bo), N, K, _stream())
+    _check(rc, "mm_fold_layernorm")
+    return q, bo
 
 
 _patch_ws: dict = {}   # device -> scratch for the staged patch rows (grown on demand, reused across calls)
@@ -397,6 +418,49 @@ def position_ids(attention_mask: torch.Tensor, input_ids: torch.Tensor | None = 
         rc = lib.mm_position_ids(_ptr(ids), _ptr(m), int(m.dtype == torch.uint8), B, S, int(attachment_id),
                                  int(tokens_per_image), int(grid), int(use_2d), _ptr(out), _ptr(status), _stream())
     _check(rc, "mm_position_ids")
+    return out
+
+
+# --------------------------------------------------------------------------------- projector training step
+def gelu_fwd(z: torch.Tensor) -> torch.Tensor:
+    _cuda(z)
+    assert z.dtype == torch.bfloat16 and z.is_contiguous()
+    a = torch.empty_like(z)
+    with _timed("mm_gelu_fwd", 4.0 * z.numel()):
+        rc = _lib.load().mm_gelu_fwd(_ptr(z), _ptr(a), z.numel(), _stream())
+    _check(rc, "mm_gelu_fwd")
+    return a
+
+
+def gelu_bwd_colsum(da: torch.Tensor, z: torch.Tensor | None):
+    """-> (dz bf16 [M,N] | None, bias_grad fp32 [N]);  z None: column sum of `da` only."""
+    _cuda(da, z)
+    lib = _lib.load()
+    assert da.dtype == torch.bfloat16 and da.is_contiguous() and da.dim() == 2
+    M, N = da.shape
+    dz = None
+    if z is not None:
+        assert z.shape == da.shape and z.dtype == torch.bfloat16 and z.is_contiguous()
+        dz = torch.empty_like(da)
+    bg = torch.empty(N, dtype=torch.float32, device=da.device)
+    ws = torch.empty(max(256, int(lib.mm_colsum_workspace_bytes(M, N))), dtype=torch.uint8, device=da.device)
+    global LAUNCHES
+    LAUNCHES += 1
+    with _timed("mm_gelu_bwd_colsum", (6.0 if z is not None else 2.0) * M * N):
+        rc = lib.mm_gelu_bwd_colsum(_ptr(da), _ptr(z), _ptr(dz), _ptr(bg), _ptr(ws), M, N, _stream())
+    _check(rc, "mm_gelu_bwd_colsum")
+    return dz, bg
+
+
+def transpose(x: torch.Tensor) -> torch.Tensor:
+    """[R, C] bf16 -> contiguous [C, R]."""
+    _cuda(x)
+    assert x.dtype == torch.bfloat16 and x.is_contiguous() and x.dim() == 2
+    R, C = x.shape
+    out = torch.empty(C, R, dtype=torch.bfloat16, device=x.device)
+    with _timed("mm_transpose", 4.0 * R * C):
+        rc = _lib.load().mm_transpose(_ptr(x), _ptr(out), R, C, _stream())
+    _check(rc, "mm_transpose")
     return out
 
 

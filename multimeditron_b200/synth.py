@@ -68,6 +68,30 @@ def make_modality_state_dict(cfg: TowerConfig, llm_hidden: int, seed: int = 0, d
     return _draw(tower_keys(cfg) + projector_keys(cfg.hidden_size, llm_hidden), gen, dtype, device)
 
 
+def add_massive_activations(sd: dict, cfg: TowerConfig, seed: int = 0, frac: float = 0.03) -> dict:
+    """Trained CLIP/SigLIP towers carry a few residual-stream channels whose magnitude is 50-200x the rest ("massive
+    activations"); random-init towers do not, so the LayerNorm statistics (E[x^2]-mean^2 in the folded GEMMs) are never
+    stressed.  This plants them: `frac` of the channels get a large constant offset (+-U(50,200)) and a x U(5,20) gain at
+    the point where the residual stream is born (CLIP: pre_layrnorm gamma/beta; SigLIP: the position embedding)."""
+    g = torch.Generator().manual_seed(seed)
+    D = cfg.hidden_size
+    n = max(1, int(round(frac * D)))
+    ch = torch.randperm(D, generator=g)[:n]
+    off = (50.0 + 150.0 * torch.rand(n, generator=g)) * (torch.randint(0, 2, (n,), generator=g) * 2 - 1)
+    gain = 5.0 + 15.0 * torch.rand(n, generator=g)
+    out = dict(sd)
+    if cfg.kind == "clip":
+        w, b = sd[VM + "pre_layrnorm.weight"].clone(), sd[VM + "pre_layrnorm.bias"].clone()
+        w[ch] = (w[ch].float() * gain).to(w.dtype)
+        b[ch] = (b[ch].float() + off).to(b.dtype)
+        out[VM + "pre_layrnorm.weight"], out[VM + "pre_layrnorm.bias"] = w, b
+    else:
+        pos = sd[VM + "embeddings.position_embedding.weight"].clone()
+        pos[:, ch] = (pos[:, ch].float() * gain + off).to(pos.dtype)
+        out[VM + "embeddings.position_embedding.weight"] = pos
+    return out
+
+
 def make_moe_state_dict(towers, llm_hidden: int, per_expert_projector: bool, seed: int = 0, dtype=torch.float32,
                         device="cpu"):
     """State dict of a MoE modality (image_modality_moe.py / image_modality_moe_pep.py): `experts.<i>.*` holds the HF

@@ -12,11 +12,12 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (B200); run with -m gpu on the GPU box")
-    config.addinivalue_line("markers", "needs_reference: needs /root/reference (build container only)")
+    config.addinivalue_line("markers", "needs_reference: needs the reference package (/root/reference, or oracle/_ref staged by oracle/build_ref.py)")
 
 
 def pytest_collection_modifyitems(config, items):
-    have_ref = os.path.isdir("/root/reference/src/multimeditron")
+    from oracle import ref_shim
+    have_ref = ref_shim.available()   # /root/reference (build container) or the staged copy under oracle/_ref (GPU box)
     try:
         import torch
         have_gpu = torch.cuda.is_available()
@@ -24,7 +25,7 @@ def pytest_collection_modifyitems(config, items):
         have_gpu = False
     for item in items:
         if "needs_reference" in item.keywords and not have_ref:
-            item.add_marker(pytest.mark.skip(reason="/root/reference not present on this machine"))
+            item.add_marker(pytest.mark.skip(reason="reference not present (neither /root/reference nor oracle/_ref)"))
         if "gpu" in item.keywords and not have_gpu:
             item.add_marker(pytest.mark.skip(reason="no CUDA device"))
 

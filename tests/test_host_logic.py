@@ -66,7 +66,9 @@ def test_config_roundtrip_and_processor_contract():
         m([px])  # no weights loaded -> loud failure, never a CPU fallback
     m.freeze_modality_embedder()
     with pytest.raises(NotImplementedError):
-        m.unfreeze_projection()
+        m.unfreeze_modality_embedder()   # ViT backward is not built; the projector's is (tests/test_train_gpu.py)
+    with pytest.raises(RuntimeError):
+        m.unfreeze_projection()          # no weights loaded yet
 
 
 def test_embedder_modality_lookup_errors():

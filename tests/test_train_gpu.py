@@ -1,0 +1,180 @@
+"""-m gpu: the projector's training step on the kernels and the small kernels around it.
+
+Reference: MLPProjector (model/projectors/mlp.py:33-39) under torch.autograd, as the ALIGNMENT stage runs it
+(model/model.py:310-326).  Ground truth = autograd through oracle.vit_oracle.mlp_projector in fp32 on the GPU; the
+reference's own bf16 regime gives the error scale.  Tolerance: |g - g32| <= 2 x |g_bf16 - g32| + 1e-2 * max|g32|.
+"""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from multimeditron_b200 import autograd_ops, ops, synth
+from multimeditron_b200.configs import TOWERS
+from multimeditron_b200.modalities import AutoModality
+from multimeditron_b200.model import B200MultiModalEmbedder
+from oracle import vit_oracle
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _close(got, ref, tol=2e-2, ulp=1.6e-2):
+    got, ref = got.float(), ref.float()
+    bound = tol * ref.abs().max() + ulp * ref.abs()
+    bad = (got - ref).abs() > bound
+    assert not bad.any(), f"{int(bad.sum())} elements off, max err {(got - ref).abs().max():.3e}, scale {ref.abs().max():.3e}"
+
+
+@pytest.mark.parametrize("R,C", [(64, 64), (72, 200), (1000, 1024), (4096, 1152), (147_456 // 8, 4096)])
+def test_transpose_bit_exact(R, C):
+    x = torch.randn(R, C, device=DEV).bfloat16()
+    assert torch.equal(ops.transpose(x), x.t().contiguous())
+
+
+@pytest.mark.parametrize("n", [8, 4096, 577 * 4096])
+def test_gelu_fwd_matches_fused_epilogue_and_torch(n):
+    z = (torch.randn(n, device=DEV) * 3).bfloat16()
+    a = ops.gelu_fwd(z)
+    _close(a, F.gelu(z.float()), tol=1e-3, ulp=8e-3)
+    if n % 256 == 0:   # bit-identical to the GEMM's fused erf-GELU epilogue: identity weight, zero bias
+        K = 256
+        zz = z.view(-1, K)[:300].contiguous()
+        eye = torch.eye(K, device=DEV).bfloat16()
+        fused = ops.gemm_bias_act(zz, eye, None, act=ops.ACT_GELU_ERF)
+        assert torch.equal(fused, ops.gelu_fwd(zz))
+
+
+@pytest.mark.parametrize("M,N", [(8, 8), (301, 264), (5000, 1024), (4617, 4096)])
+def test_gelu_bwd_and_column_sums(M, N):
+    g = torch.Generator(device=DEV).manual_seed(M + N)
+    da = torch.randn(M, N, device=DEV, generator=g).bfloat16()
+    z = (torch.randn(M, N, device=DEV, generator=g) * 2).bfloat16()
+    dz, db = ops.gelu_bwd_colsum(da, z)
+    zf = z.float().requires_grad_(True)
+    F.gelu(zf).backward(da.float())
+    _close(dz, zf.grad, tol=1e-3, ulp=8e-3)
+    want = dz.float().sum(0)                       # the sum runs over the stored bf16 values
+    assert torch.allclose(db, want, rtol=1e-4, atol=1e-3 * max(1.0, M ** 0.5))
+    dz2, db2 = ops.gelu_bwd_colsum(da, z)
+    assert torch.equal(db, db2) and torch.equal(dz, dz2)     # deterministic
+    none, cs = ops.gelu_bwd_colsum(da, None)
+    assert none is None and torch.allclose(cs, da.float().sum(0), rtol=1e-4, atol=1e-3 * max(1.0, M ** 0.5))
+
+
+def test_gather_rows_is_the_scatter_backward():
+    H, n_dest, n = 512, 4000, 1500
+    src = torch.randn(n_dest, H, device=DEV).bfloat16()
+    rows = torch.randperm(n_dest, device=DEV)[:n].to(torch.int32)
+    assert torch.equal(ops.gather_rows(src, rows), src[rows.long()])
+    assert torch.equal(ops.gather_rows(src, rows, out_dtype=torch.float32), src[rows.long()].float())
+    st = ops.new_status(DEV)
+    rows[3] = n_dest
+    ops.gather_rows(src, rows, status=st)
+    with pytest.raises(IndexError):
+        ops.raise_for_status(st)
+
+
+def test_embed_gather_skip_leaves_attachment_rows_alone():
+    V, H, att = 300, 256, 296
+    table = torch.randn(V, H, device=DEV).bfloat16()
+    ids = torch.randint(0, V - 8, (4, 50), device=DEV)
+    ids[:, 10:30] = att
+    full = ops.embed_gather(table, ids)
+    part = ops.embed_gather(table, ids, skip_id=att)
+    keep = ids != att
+    assert torch.equal(part[keep], full[keep]) and torch.equal(full[~keep], table[att].expand(int((~keep).sum()), H))
+
+
+@pytest.mark.parametrize("N,K", [(256, 128), (3072, 1024), (4304, 1152), (1152, 4304)])
+def test_fold_layernorm_kernel(N, K):
+    g0 = torch.Generator().manual_seed(N + K)
+    w = (torch.randn(N, K, generator=g0) * 0.02).bfloat16().to(DEV)
+    b = (torch.randn(N, generator=g0) * 0.02).bfloat16().to(DEV)
+    gamma = (1 + 0.1 * torch.randn(K, generator=g0)).bfloat16().to(DEV)
+    beta = (0.1 * torch.randn(K, generator=g0)).bfloat16().to(DEV)
+    q, bo = ops.fold_layernorm(w, b, gamma, beta)
+    wg = w.double() * gamma.double()[None]
+    wg = wg - wg.mean(1, keepdim=True)
+    ulp = wg.abs().max().item() * 2 ** -8
+    assert (q.double() - wg).abs().max().item() <= 1.01 * ulp            # each element within one bf16 ulp (error feedback)
+    assert q.double().sum(1).abs().max().item() <= 1.01 * ulp            # ... and the ROW SUMS stay within one ulp of zero
+    want_b = (w.double() @ beta.double() + b.double())
+    assert (bo.double() - want_b).abs().max().item() <= want_b.abs().max().item() * 2 ** -8
+
+
+@pytest.mark.parametrize("M,D,H", [(98, 128, 64), (8 * 49, 768, 512), (4 * 576, 1024, 4096)])
+def test_projector_forward_backward_vs_fp32_autograd(M, D, H):
+    sd = {k: v.to(DEV) for k, v in synth._draw(synth.projector_keys(D, H), torch.Generator().manual_seed(M), torch.float32, "cpu").items()}
+    x = torch.randn(M, D, device=DEV) * 0.7
+    dy = torch.randn(M, H, device=DEV) * 0.1
+    names = [f"projector.projection.{i}.{n}" for i in (0, 2, 4) for n in ("weight", "bias")]
+
+    def run(dtype):
+        p = {k: sd[k].to(dtype).requires_grad_(True) for k in names}
+        xx = x.to(dtype).requires_grad_(True)
+        y = vit_oracle.mlp_projector(p, xx)
+        y.backward(dy.to(dtype))
+        return y.detach().float(), [xx.grad.float()] + [p[k].grad.float() for k in names]
+
+    y32, g32 = run(torch.float32)
+    ybf, gbf = run(torch.bfloat16)
+    params = [sd[k].bfloat16().requires_grad_(True) for k in names]
+    xb = x.bfloat16().requires_grad_(True)
+    y = autograd_ops.ProjectorFunction.apply(xb, *params)
+    # forward: identical rounding points to the inference path (fused GELU epilogues)
+    a = ops.gemm_bias_act(xb.detach(), params[0].detach(), params[1].detach(), act=ops.ACT_GELU_ERF)
+    a = ops.gemm_bias_act(a, params[2].detach(), params[3].detach(), act=ops.ACT_GELU_ERF)
+    assert torch.equal(y.detach(), ops.gemm_bias_act(a, params[4].detach(), params[5].detach()))
+    y.backward(dy.bfloat16())
+    got = [xb.grad.float()] + [p.grad.float() for p in params]
+    _close(y.detach(), y32)
+    for name, g, r32, rbf in zip(["x"] + names, got, g32, gbf):
+        scale = r32.abs().max().item()
+        err, ref_err = (g - r32).abs().max().item(), (rbf - r32).abs().max().item()
+        print(f"[projector bwd M={M} D={D} H={H}] {name}: max-abs {err:.3e} (torch bf16 autograd: {ref_err:.3e}) /absmax {err / scale:.3e}")
+        assert err <= 2.0 * ref_err + 1e-2 * scale, name
+
+
+def test_embedder_alignment_step_mirror_class():
+    """The repo's own mirror (no reference installed): unfreeze_projection() exposes nn.Parameters that share storage
+    with the kernel-side weights; one forward+backward through embed_modalities_with_text, then an SGD step that the
+    next (inference) forward must see."""
+    cfg = TOWERS["tiny"]
+    H, V, B, S = 64, 300, 2, 48
+    sd = synth.make_modality_state_dict(cfg, H, seed=2)
+    m = AutoModality.from_config(AutoModality.config_from_dict(
+        {"model_type": "meditron_clip_b200", "hidden_size": H, "clip_name": "tiny"})).load_reference_state_dict(sd, DEV)
+    att = V - 4
+    ids, _ = synth.make_sequences(B, S, 1, cfg.num_patches, V - 4, att, V - 3, V - 2, V - 1, seed=1)
+    px = synth.make_pixels(cfg, B, seed=1)
+    pmi = {"stacked": {"image": [px[i] for i in range(B)]}, "batch_idx": {}, "token_range": {}}
+    table = (torch.randn(V, H, generator=torch.Generator().manual_seed(3)) * 0.02).bfloat16().to(DEV)
+    emb = B200MultiModalEmbedder(table, [m], att)
+    with torch.no_grad():
+        base = emb(ids, pmi, positions_from="device").clone()
+    m.unfreeze_projection()
+    assert sorted(k for k, _ in m.named_parameters()) == sorted(
+        f"projector.projection.{i}.{n}" for i in (0, 2, 4) for n in ("weight", "bias"))
+    out = emb(ids, pmi, positions_from="device")
+    emb.check()
+    assert out.requires_grad and torch.equal(out.detach(), base)          # same bits as the fused inference path
+    w = torch.randn_like(out)
+    (out.float() * w.float()).sum().backward()
+    # reference gradient: fp32 autograd through the oracle projector on the same features
+    with torch.no_grad():
+        feats = m.runner.features(px.to(DEV)).float()
+    p32 = {k: v.to(DEV).float().requires_grad_(True) for k, v in sd.items() if k.startswith("projector.")}
+    y = vit_oracle.mlp_projector(p32, feats)
+    rows = (ids.to(DEV).view(-1) == att).nonzero().squeeze(1)
+    y.backward(w.view(-1, H)[rows].float())
+    for k, p in m.named_parameters():
+        r = p32[k].grad
+        err, scale = (p.grad.float() - r).abs().max().item(), r.abs().max().item()
+        assert err <= 3e-2 * scale + 1e-6, (k, err, scale)
+    with torch.no_grad():
+        for p in m.parameters():
+            p -= 0.5 * p.grad
+    m.freeze_projection()
+    with torch.no_grad():
+        after = emb(ids, pmi, positions_from="device")
+    assert not torch.equal(after, base)                                    # the kernels multiply by the updated weights
