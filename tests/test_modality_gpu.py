@@ -105,9 +105,12 @@ def test_count_mismatch_is_detected_not_truncated():
     ids, pmi, att, _ = _make_batch(2, 64, 2, cfg, 300, 6, "right")
     ids[0, (ids[0] == att).nonzero()[0]] = 1   # one attachment token fewer than modality rows
     e = B200MultiModalEmbedder(torch.zeros(300, 64, device=DEV).bfloat16(), [m], att)
-    e(ids, pmi, positions_from="device")
+    with pytest.raises(RuntimeError):          # HOST ids (the collator's format): verified eagerly, before any launch
+        e(ids, pmi, positions_from="device")
+    e(ids.to(DEV), pmi, positions_from="device")   # DEVICE ids: lazy, one sync in check()
     with pytest.raises(RuntimeError):
         e.check()
+    e.check()                                  # the status word was cleared: one bad batch does not poison later checks
     pmi["batch_idx"]["image"] = pmi["batch_idx"]["image"][:-1]
     pmi["token_range"]["image"] = pmi["token_range"]["image"][:-1]
     e2 = B200MultiModalEmbedder(torch.zeros(300, 64, device=DEV).bfloat16(), [m], att, fuse_splice=False)
