@@ -95,9 +95,11 @@ def test_fold_layernorm_kernel(N, K):
     q, bo = ops.fold_layernorm(w, b, gamma, beta)
     wg = w.double() * gamma.double()[None]
     wg = wg - wg.mean(1, keepdim=True)
-    ulp = wg.abs().max().item() * 2 ** -8
-    assert (q.double() - wg).abs().max().item() <= 1.01 * ulp            # each element within one bf16 ulp (error feedback)
-    assert q.double().sum(1).abs().max().item() <= 1.01 * ulp            # ... and the ROW SUMS stay within one ulp of zero
+    import math
+    ulp = 2.0 ** (math.floor(math.log2(wg.abs().max().item())) - 7)      # bf16 spacing in the binade of the largest |w|
+    # sigma-delta rounding: |q - wg| <= |q - t| + |carried error| <= ulp/2 + ulp/2
+    assert (q.double() - wg).abs().max().item() <= 1.01 * ulp
+    assert q.double().sum(1).abs().max().item() <= 0.51 * ulp + 1e-6     # ... and the ROW SUMS stay within half an ulp of zero
     want_b = (w.double() @ beta.double() + b.double())
     assert (bo.double() - want_b).abs().max().item() <= want_b.abs().max().item() * 2 ** -8
 
@@ -110,8 +112,8 @@ def test_projector_forward_backward_vs_fp32_autograd(M, D, H):
     names = [f"projector.projection.{i}.{n}" for i in (0, 2, 4) for n in ("weight", "bias")]
 
     def run(dtype):
-        p = {k: sd[k].to(dtype).requires_grad_(True) for k in names}
-        xx = x.to(dtype).requires_grad_(True)
+        p = {k: sd[k].detach().clone().to(dtype).requires_grad_(True) for k in names}     # fresh leaves per dtype
+        xx = x.detach().clone().to(dtype).requires_grad_(True)
         y = vit_oracle.mlp_projector(p, xx)
         y.backward(dy.to(dtype))
         return y.detach().float(), [xx.grad.float()] + [p[k].grad.float() for k in names]
