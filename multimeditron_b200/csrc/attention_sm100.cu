@@ -33,6 +33,26 @@ constexpr int kMaxStages = 8;
 #define MM_ATTN_POLL_NS 32
 #endif
 constexpr unsigned kPollSleepNs = MM_ATTN_POLL_NS;  // idle back-off of the two polling service threads
+// MM_ATTN_TOKEN=1: the two streams take turns in the exp phase (named-barrier token).  Measured (tools/micro/
+// tmem_probe2): a lone warp per scheduler sustains 10.5 clk per ex2, two interleaved warps 8.7 — so the default lets
+// both streams run their exp phases freely and the token survives only as an A/B switch.
+#ifndef MM_ATTN_TOKEN
+#define MM_ATTN_TOKEN 1
+#endif
+// MM_ATTN_STALE_MAX=1: from the second kv tile on, the exps of a tile use the reference max decided by the PREVIOUS
+// tiles (known before S even arrives); the tile's own row max is computed next to the exps (FMNMX3 on the ALU pipe,
+// hidden under the MUFU-bound exp stream) and only feeds the NEXT tile's decision.  P <= 2^kRedoThreshold is
+// harmless (bf16 P and the fp32 O / row sum have the exponent range); beyond it the tile's exps are redone with the
+// tile max (never taken on real data: the reference already is a max over >= 128 keys).
+#ifndef MM_ATTN_STALE_MAX
+#define MM_ATTN_STALE_MAX 0
+#endif
+// MM_ATTN_PACKED=1: the scale-and-shift before each ex2 and the row-sum adds run as packed fp32x2 instructions
+// (FFMA2 / FADD2): 2.5 instead of 3.5 issue slots per score in the exp phase.
+#ifndef MM_ATTN_PACKED
+#define MM_ATTN_PACKED 1
+#endif
+constexpr float kRedoThreshold = 60.0f;   // log2 units
 
 template <int HD, int BKV>
 struct AttnCfg {
@@ -98,6 +118,45 @@ __device__ __forceinline__ float ex2(float x) {
   return y;
 }
 
+// exp phase of 4 adjacent scores: p = 2^(s*sl2 - m), two packed bf16x2 words out, row sums kept as two fp32x2 pairs
+struct ExpAcc {
+  uint64_t sa, sb;     // packed partial row sums (MM_ATTN_PACKED)
+  float s0, s1, s2, s3;
+};
+__device__ __forceinline__ void exp4(const uint32_t* sv, uint32_t* pk, float sl2, float m_scaled, ExpAcc& a) {
+#if MM_ATTN_PACKED
+  const uint64_t k2 = f32x2(sl2, sl2), nm2 = f32x2(-m_scaled, -m_scaled);
+  float x0, x1, x2, x3;
+  f32x2_unpack(fma_f32x2(f32x2(__uint_as_float(sv[0]), __uint_as_float(sv[1])), k2, nm2), x0, x1);
+  f32x2_unpack(fma_f32x2(f32x2(__uint_as_float(sv[2]), __uint_as_float(sv[3])), k2, nm2), x2, x3);
+  const float p0 = ex2(x0), p1 = ex2(x1), p2 = ex2(x2), p3 = ex2(x3);
+  a.sa = add_f32x2(a.sa, f32x2(p0, p1));
+  a.sb = add_f32x2(a.sb, f32x2(p2, p3));
+#else
+  const float p0 = ex2(fmaf(__uint_as_float(sv[0]), sl2, -m_scaled));
+  const float p1 = ex2(fmaf(__uint_as_float(sv[1]), sl2, -m_scaled));
+  const float p2 = ex2(fmaf(__uint_as_float(sv[2]), sl2, -m_scaled));
+  const float p3 = ex2(fmaf(__uint_as_float(sv[3]), sl2, -m_scaled));
+  a.s0 += p0, a.s1 += p1, a.s2 += p2, a.s3 += p3;
+#endif
+  pk[0] = pack_bf16x2(p0, p1);
+  pk[1] = pack_bf16x2(p2, p3);
+}
+__device__ __forceinline__ void exp_acc_reset(ExpAcc& a) {
+  a.sa = a.sb = 0ull;
+  a.s0 = a.s1 = a.s2 = a.s3 = 0.f;
+}
+__device__ __forceinline__ float exp_acc_total(const ExpAcc& a) {
+#if MM_ATTN_PACKED
+  float u0, u1, u2, u3;
+  f32x2_unpack(a.sa, u0, u1);
+  f32x2_unpack(a.sb, u2, u3);
+  return (u0 + u1) + (u2 + u3);
+#else
+  return (a.s0 + a.s1) + (a.s2 + a.s3);
+#endif
+}
+
 // D[tmem] (+)= A[tmem] * B[smem desc]
 __device__ __forceinline__ void tc_mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
                                               uint32_t accumulate) {
@@ -144,6 +203,19 @@ __device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
       : "r"(smem_u32(bar)), "r"(parity)
       : "memory");
   return ok != 0;
+}
+// softmax-side wait: MM_ATTN_SPIN=1 polls with the non-blocking test_wait (243 clk ping-pong round trip measured)
+// instead of try_wait (375 clk: the hardware suspends the thread for a time slice)
+#ifndef MM_ATTN_SPIN
+#define MM_ATTN_SPIN 0
+#endif
+__device__ __forceinline__ void sm_wait(uint64_t* bar, uint32_t parity) {
+#if MM_ATTN_SPIN
+  while (!mbar_test(bar, parity)) {
+  }
+#else
+  mbar_wait(bar, parity);
+#endif
 }
 __device__ __forceinline__ void named_bar_sync(int id, int count) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
@@ -406,25 +478,32 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     TRACE_DECL
     // one token per scheduler (warp q of stream 0 and warp q of stream 1 share scheduler q): barriers 1 + 2q + s
     const int tok_mine = 1 + 2 * q + s, tok_other = 1 + 2 * q + (s ^ 1);
+#if MM_ATTN_TOKEN
     if (s == 1) named_bar_arrive(tok_other, 64);  // stream 0 goes first
+#else
+    (void)tok_mine, (void)tok_other;
+#endif
     for (int g = 0; g < sc.ngroups; ++g) {
       const int u = blockIdx.x + sc.unit_ord(g) * gridDim.x;
       const int b = u / p.heads, h = u - b * p.heads;
       const int nt = sc.ntiles(s, g);
       for (int j = 0; j < sc.slots(g); ++j) {
         if (j >= nt) {  // no tile in this slot: keep the token moving
+#if MM_ATTN_TOKEN
           for (int kt = 0; kt < nkv; ++kt) {
             named_bar_sync(tok_mine, 64);
             named_bar_arrive(tok_other, 64);
           }
+#endif
           continue;
         }
         const int qt = sc.first_qt(s, g) + 2 * j;
         const bool warp_live = qt * kBQ + q * 32 < p.T;  // warps whose 32 rows are all padding only keep the protocol
         float m_run = -INFINITY, l_run = 0.f;            // running max (raw score units) and row sum
+        float m_next = -INFINITY;                        // reference max the NEXT kv tile will use (stale-max mode)
         for (int kt = 0; kt < nkv; ++kt, ++it) {
           const int valid = p.T - kt * BKV;  // columns >= valid are padding (only in the last kv tile)
-          mbar_wait(&bars->s_full[s], it & 1);
+          sm_wait(&bars->s_full[s], it & 1);
           TRACE_SM(0);
           tc_fence_after();
           uint32_t sv[BKV];
@@ -442,42 +521,49 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
           uint32_t pk[BKV / 2];
           float m_new = m_run, sum = 0.f;
           float m_scaled = 0.f;
+          const bool stale = MM_ATTN_STALE_MAX && kt > 0;   // reference max already decided by the previous tiles
           if (warp_live) {
             if (valid < BKV) {
 #pragma unroll
               for (int jj = 0; jj < BKV; ++jj)
                 if (jj >= valid) sv[jj] = 0xff800000u;  // -inf
             }
-            float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+            if (!stale) {
+              float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-            for (int jj = 0; jj < BKV; jj += 8) {
-              mx0 = fmaxf(mx0, fmaxf(__uint_as_float(sv[jj + 0]), __uint_as_float(sv[jj + 1])));
-              mx1 = fmaxf(mx1, fmaxf(__uint_as_float(sv[jj + 2]), __uint_as_float(sv[jj + 3])));
-              mx2 = fmaxf(mx2, fmaxf(__uint_as_float(sv[jj + 4]), __uint_as_float(sv[jj + 5])));
-              mx3 = fmaxf(mx3, fmaxf(__uint_as_float(sv[jj + 6]), __uint_as_float(sv[jj + 7])));
+              for (int jj = 0; jj < BKV; jj += 8) {
+                mx0 = fmaxf(mx0, fmaxf(__uint_as_float(sv[jj + 0]), __uint_as_float(sv[jj + 1])));
+                mx1 = fmaxf(mx1, fmaxf(__uint_as_float(sv[jj + 2]), __uint_as_float(sv[jj + 3])));
+                mx2 = fmaxf(mx2, fmaxf(__uint_as_float(sv[jj + 4]), __uint_as_float(sv[jj + 5])));
+                mx3 = fmaxf(mx3, fmaxf(__uint_as_float(sv[jj + 6]), __uint_as_float(sv[jj + 7])));
+              }
+              const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+              // the reference max only moves when it grows by more than the threshold (keeps O rescales rare)
+              if ((mx - m_run) * sl2 > kRescaleThreshold) m_new = mx;  // also true for m_run = -inf
+            } else {
+              m_new = m_next;
             }
-            const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-            // the reference max only moves when it grows by more than the threshold (keeps O rescales rare)
-            if ((mx - m_run) * sl2 > kRescaleThreshold) m_new = mx;  // also true for m_run = -inf
             m_scaled = m_new * sl2;
           }
           TRACE_SM(14);
+#if MM_ATTN_TOKEN
           named_bar_sync(tok_mine, 64);  // ---- exp phase: this warp's turn on its scheduler's MUFU ----
+#endif
           TRACE_SM(15);
           if (warp_live) {
-            float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
+            ExpAcc ea;
+            exp_acc_reset(ea);
+            float tx0 = -INFINITY, tx1 = -INFINITY;   // this tile's own row max (feeds the next tile's decision)
             if (valid >= BKV) {
               // full tile: one straight-line block, so that ptxas interleaves the ex2 of the whole row (a block per
               // 32-column chunk drains the MUFU pipe at every boundary: measured 1900 vs 1250 clk per tile)
 #pragma unroll
               for (int jj = 0; jj < BKV; jj += 4) {
-                const float p0 = ex2(fmaf(__uint_as_float(sv[jj + 0]), sl2, -m_scaled));
-                const float p1 = ex2(fmaf(__uint_as_float(sv[jj + 1]), sl2, -m_scaled));
-                const float p2 = ex2(fmaf(__uint_as_float(sv[jj + 2]), sl2, -m_scaled));
-                const float p3 = ex2(fmaf(__uint_as_float(sv[jj + 3]), sl2, -m_scaled));
-                sum0 += p0, sum1 += p1, sum2 += p2, sum3 += p3;
-                pk[jj >> 1] = pack_bf16x2(p0, p1);
-                pk[(jj >> 1) + 1] = pack_bf16x2(p2, p3);
+                exp4(sv + jj, pk + (jj >> 1), sl2, m_scaled, ea);
+                if (MM_ATTN_STALE_MAX) {
+                  tx0 = fmaxf(tx0, fmaxf(__uint_as_float(sv[jj + 0]), __uint_as_float(sv[jj + 1])));
+                  tx1 = fmaxf(tx1, fmaxf(__uint_as_float(sv[jj + 2]), __uint_as_float(sv[jj + 3])));
+                }
               }
             } else {
               // last (partial) kv tile: chunks that are all padding are skipped
@@ -486,13 +572,11 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
                 if (c * 32 < valid) {
 #pragma unroll
                   for (int jj = c * 32; jj < c * 32 + 32; jj += 4) {
-                    const float p0 = ex2(fmaf(__uint_as_float(sv[jj + 0]), sl2, -m_scaled));
-                    const float p1 = ex2(fmaf(__uint_as_float(sv[jj + 1]), sl2, -m_scaled));
-                    const float p2 = ex2(fmaf(__uint_as_float(sv[jj + 2]), sl2, -m_scaled));
-                    const float p3 = ex2(fmaf(__uint_as_float(sv[jj + 3]), sl2, -m_scaled));
-                    sum0 += p0, sum1 += p1, sum2 += p2, sum3 += p3;
-                    pk[jj >> 1] = pack_bf16x2(p0, p1);
-                    pk[(jj >> 1) + 1] = pack_bf16x2(p2, p3);
+                    exp4(sv + jj, pk + (jj >> 1), sl2, m_scaled, ea);
+                    if (MM_ATTN_STALE_MAX) {
+                      tx0 = fmaxf(tx0, fmaxf(__uint_as_float(sv[jj + 0]), __uint_as_float(sv[jj + 1])));
+                      tx1 = fmaxf(tx1, fmaxf(__uint_as_float(sv[jj + 2]), __uint_as_float(sv[jj + 3])));
+                    }
                   }
                 } else {
 #pragma unroll
@@ -500,13 +584,29 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
                 }
               }
             }
-            sum = (sum0 + sum1) + (sum2 + sum3);
+            sum = exp_acc_total(ea);
+            if (MM_ATTN_STALE_MAX) {
+              const float tx = fmaxf(tx0, tx1);
+              const float over = (tx - m_new) * sl2;   // how far this tile's own max sits above the reference used
+              m_next = over > kRescaleThreshold ? tx : m_new;
+              if (stale && __any_sync(0xffffffffu, over > kRedoThreshold)) {
+                // the stale reference was far too low for this tile (P would leave the safe range): redo the row
+                // with the tile max — rows below the redo threshold keep their reference (identical results)
+                if (over > kRedoThreshold) m_new = tx, m_scaled = tx * sl2;
+                exp_acc_reset(ea);
+#pragma unroll
+                for (int jj = 0; jj < BKV; jj += 4) exp4(sv + jj, pk + (jj >> 1), sl2, m_scaled, ea);
+                sum = exp_acc_total(ea);
+              }
+            }
           }
           TRACE_SM(2);
+#if MM_ATTN_TOKEN
           named_bar_arrive(tok_other, 64);  // ---- token to the other stream's warp on this scheduler ----
+#endif
           // P (TMEM) and the O accumulator are free once PV of the previous iteration retired
           if (it > 0) {
-            mbar_wait(&bars->pv_done[s], (it - 1) & 1);
+            sm_wait(&bars->pv_done[s], (it - 1) & 1);
             tc_fence_after();
           }
           TRACE_SM(3);
@@ -541,7 +641,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
           TRACE_SM(5);
         }
         // ---- epilogue of the q tile: O / l -> bf16 -> global ----
-        mbar_wait(&bars->pv_done[s], (it - 1) & 1);
+        sm_wait(&bars->pv_done[s], (it - 1) & 1);
         tc_fence_after();
         if (warp_live) {
           const float inv_l = 1.0f / l_run;
@@ -572,7 +672,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         if (lane == 0) mbar_arrive(&bars->o_empty[s]);
       }
     }
+#if MM_ATTN_TOKEN
     if (s == 0) named_bar_sync(tok_mine, 64);  // absorb stream 1's last token pass
+#endif
   }
 
   tc_fence_before();

@@ -250,6 +250,32 @@ def test_attention_peaked_rows_rescale():
     close(out, ref, tol=1e-2)
 
 
+@pytest.mark.parametrize("T,hd,jump_at", [(577, 64, 256), (577, 64, 130), (729, 72, 480), (300, 64, 290)])
+def test_attention_score_jump_beyond_the_stale_reference(T, hd, jump_at):
+    """From the second kv tile on the exps use the reference max decided by the EARLIER tiles (stale max).  Here the
+    scores jump by > 100 log2 units at key `jump_at`: rows must take the redo path (tile re-exponentiated with its own
+    max) instead of overflowing, and rows whose jump stays below the redo threshold must rescale on the next tile."""
+    B, nh = 2, 2
+    hs = ops.attn_head_stride(hd)
+    g0 = torch.Generator().manual_seed(T + hd)
+    x = torch.randn(B * T, 3, nh, hd, generator=g0) * 0.3
+    x[:, 0] += 1.0                                            # q ~ ones
+    t = torch.arange(B * T) % T
+    big = (t >= jump_at).float().view(-1, 1, 1)
+    x[:, 1] += big * 10.0                                     # k: +10 on every channel -> score jump ~ hd*10*scale
+    x[B * T // 2:, 1] *= 0.25                                 # second image: a jump that stays below the redo threshold
+    qkv = torch.zeros(B * T, 3, nh, hs, dtype=torch.bfloat16)
+    qkv[..., :hd] = x.bfloat16()
+    qkv = qkv.view(B * T, 3 * nh * hs).to(DEV)
+    scale = hd ** -0.5
+    out = ops.attention_fwd(qkv, B, T, nh, hd, scale)
+    assert torch.isfinite(out.float()).all()
+    xx = qkv.view(B, T, 3, nh, hs)[..., :hd].float()
+    q, k, v = [xx[:, :, i].transpose(1, 2) for i in range(3)]
+    ref = F.scaled_dot_product_attention(q, k, v, scale=scale).transpose(1, 2).reshape(B * T, nh * hd)
+    close(out, ref, tol=1e-2)
+
+
 def test_attention_rejects_unsupported_shapes():
     qkv = torch.zeros(8, 3 * 96, device=DEV).bfloat16()
     with pytest.raises(ops.MMError):

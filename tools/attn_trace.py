@@ -6,9 +6,10 @@ import ctypes as C, os, subprocess, sys
 import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 src = os.path.join(ROOT, "multimeditron_b200", "csrc")
-so = "/tmp/libmm_trace.so"
-files = ["lib.cu", "splice.cu", "layernorm.cu", "gemm_sm100.cu", "attention_sm100.cu", "moe_fuse.cu", "preprocess.cu"]
-subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-DMM_ATTN_TRACE",
+so = os.environ.get("MM_TRACE_LIB", "/tmp/libmm_trace.so")
+files = ["lib.cu", "splice.cu", "layernorm.cu", "gemm_sm100.cu", "attention_sm100.cu", "moe_fuse.cu", "preprocess.cu", "train_ops.cu"]
+if not os.environ.get("MM_TRACE_LIB"):
+  subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-DMM_ATTN_TRACE",
                        "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-shared", "-o", so, "-cudart", "static"]
                       + [os.path.join(src, f) for f in files])
 lib = C.CDLL(so)
