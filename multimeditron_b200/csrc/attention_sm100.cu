@@ -728,13 +728,21 @@ static int launch_attention(const void* qkv, const AttnParams& p, cudaStream_t s
 }
 }  // namespace mm
 
+namespace mm {
+int launch_attention3(const void* qkv, void* out, int B, int T, int heads, float scale, cudaStream_t st);
+}
+#ifndef MM_ATTN_V3
+#define MM_ATTN_V3 1
+#endif
 using namespace mm;
 
 #ifdef MM_ATTN_TRACE
+namespace mm { int attention3_trace_set(long long* buf); }
 extern "C" int mm_attention_trace_set(long long* buf) {
   if (cudaMemcpyToSymbol(g_attn_trace, &buf, sizeof(buf)) != cudaSuccess) return MM_ERR_CUDA;
   return MM_OK;
 }
+extern "C" int mm_attention3_trace_set(long long* buf) { return mm::attention3_trace_set(buf); }
 #endif
 
 extern "C" int64_t mm_attention_head_stride(int64_t head_dim) {
@@ -761,6 +769,10 @@ extern "C" int mm_attention_fwd(const void* qkv, void* out, int64_t B, int64_t T
   p.ld_out = (int)(heads * head_dim);
   p.scale_log2 = scale * 1.4426950408889634f;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+#if MM_ATTN_V3
+  // head_dim 64: three query streams on 64-column kv tiles (attention3_sm100.cu)
+  if (hs == 64) return launch_attention3(qkv, out, (int)B, (int)T, (int)heads, scale, st);
+#endif
   if (hs == 64) return launch_attention<64, 128>(qkv, p, st);
   return launch_attention<80, 96>(qkv, p, st);
 }
