@@ -4,8 +4,12 @@
  * One shared library (multimeditron_b200/csrc/libmm_b200.so) exports every symbol
  * declared here.  All pointers are raw DEVICE pointers owned by the caller, all
  * sizes are element counts unless named *_bytes, `stream` is a cudaStream_t passed
- * as void*.  No entry point synchronises, allocates, or keeps global mutable state;
- * every call is re-entrant across streams and devices.  Return value: MM_OK or an
+ * as void*.  No entry point synchronises, allocates, or keeps global mutable state
+ * (the only process state is write-once: per-device cudaFuncSetAttribute flags and the
+ * SM count, both behind atomics, and two environment switches read once at first use);
+ * every call is re-entrant across host threads, streams and devices.  Scratch memory is
+ * always caller-supplied, so two streams never share a buffer unless the caller hands
+ * them the same one.  Return value: MM_OK or an
  * mm_status error (host-detectable argument errors).  Data-dependent errors (an
  * index out of range, attachment-token count != number of modality rows) are
  * reported through the caller-supplied device `status` word (see mm_status_bits) so
@@ -44,7 +48,11 @@ typedef enum mm_act {
   MM_ACT_NONE = 0,
   MM_ACT_QUICK_GELU = 1,  /* x*sigmoid(1.702x)   HF:activations.py:117-123 (CLIP MLP)          */
   MM_ACT_GELU_ERF = 2,    /* exact GELU          src/multimeditron/model/projectors/mlp.py:35,37 */
-  MM_ACT_GELU_TANH = 3    /* gelu_pytorch_tanh   HF:models/siglip (hidden_act)                 */
+  MM_ACT_GELU_TANH = 3,   /* gelu_pytorch_tanh   HF:models/siglip (hidden_act)                 */
+  /* per-call tuning flag OR-ed into `act` of mm_gemm_bias_act / mm_gemm_ln_bias_act: run the 1-CTA kernel
+   * (128 x 256 tiles) instead of the default CTA-pair kernel (tcgen05 cta_group::2, 256 x 256 tiles, M > 128).
+   * Both kernels accumulate every output in the same k order: results are bit-identical (tested).            */
+  MM_GEMM_FLAG_1CTA = 0x100
 } mm_act;
 
 /* Library / build info. */
@@ -186,15 +194,6 @@ int64_t mm_gemm_row_stats_slots(int64_t N);
 int mm_fold_layernorm(const void* W, int64_t ldw, const void* bias, const void* gamma, const void* beta,
                       void* W_out, int64_t ldo, void* bias_out, int64_t N, int64_t K, void* stream);
 
-/*
- * mm_set_gemm_pair — tuning switch of mm_gemm_bias_act / mm_gemm_ln_bias_act (no reference counterpart).
- * The GEMMs run by default (M > 128) on CTA PAIRS: the two CTAs of a 2-CTA cluster compute one 256 x 256 tile with
- * tcgen05.mma.cta_group::2, each CTA staging its 128 rows of A and half of the W tile.  on = 0 forces the 1-CTA
- * kernel (128 x 256 tiles), on = 1 the pair kernel, on < 0 returns to the default (environment MM_B200_GEMM_PAIR,
- * else pair).  Both kernels accumulate every output in the same k order: results are bit-identical (tested).
- * Process-wide, not thread-safe against concurrent GEMM launches.
- */
-void mm_set_gemm_pair(int on);
 int mm_gemm_ln_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias,
                         void* C, int64_t ldc, int64_t M, int64_t N, int64_t K, int act,
                         const void* residual, int64_t ldr, const int32_t* out_row_map,

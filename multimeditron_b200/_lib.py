@@ -39,7 +39,6 @@ SIGNATURES = {
     "mm_layernorm": (i32, [vp, vp, vp, vp, i64, i64, f32, i64, i64, i64, vp]),
     "mm_gemm_bias_act": (i32, [vp, i64, vp, i64, vp, vp, i64, i64, i64, i64, i32, vp, i64, i64, i64, vp, i64, vp]),
     "mm_gemm_row_stats_slots": (i64, [i64]),
-    "mm_set_gemm_pair": (None, [i32]),
     "mm_fold_layernorm": (i32, [vp, i64, vp, vp, vp, vp, i64, vp, i64, i64, vp]),
     "mm_gemm_ln_bias_act": (i32, [vp, i64, vp, i64, vp, vp, i64, i64, i64, i64, i32, vp, i64, vp, i64, vp, vp, f32, vp]),
     "mm_patch_embed": (i32, [vp, i32, i64, i64, i64, vp, i64, vp, vp, vp, vp, i64, vp]),

@@ -30,6 +30,13 @@ class ProjectorFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w0, b0, w2, b2, w4, b4):
         xb = _bf(x)
+        M = xb.shape[0]
+        Mp = (M + 7) // 8 * 8      # the wgrad GEMMs contract over the token dimension: K must be a multiple of 8.
+        if Mp != M:                # Zero rows are appended (their dy is zero in backward: no contribution anywhere)
+            xp = torch.zeros(Mp, xb.shape[1], dtype=xb.dtype, device=xb.device)
+            xp[:M] = xb
+            xb = xp
+        ctx.rows = M
         W0, B0, W2, B2, W4, B4 = map(_bf, (w0, b0, w2, b2, w4, b4))
         z0 = ops.gemm_bias_act(xb, W0, B0)
         a0 = ops.gelu_fwd(z0)
@@ -38,13 +45,18 @@ class ProjectorFunction(torch.autograd.Function):
         y = ops.gemm_bias_act(a1, W4, B4)
         ctx.save_for_backward(xb, z0, a0, z1, a1, W0, W2, W4)
         ctx.dtypes = (x.dtype, w0.dtype, b0.dtype, w2.dtype, b2.dtype, w4.dtype, b4.dtype)
-        return y
+        return y[:M] if Mp != M else y
 
     @staticmethod
     def backward(ctx, dy):
         xb, z0, a0, z1, a1, W0, W2, W4 = ctx.saved_tensors
         need = ctx.needs_input_grad
         dyb = _bf(dy)
+        M = ctx.rows
+        if xb.shape[0] != M:
+            dp = torch.zeros(xb.shape[0], dyb.shape[1], dtype=dyb.dtype, device=dyb.device)
+            dp[:M] = dyb
+            dyb = dp
 
         def wgrad(dz, a):        # [N, K] = dzᵀ[N, M] · a[M, K]  ->  GEMM(A = dzᵀ, "W" = aᵀ)
             return ops.gemm_bias_act(ops.transpose(dz), ops.transpose(a))
@@ -61,6 +73,8 @@ class ProjectorFunction(torch.autograd.Function):
         dz0, db0 = ops.gelu_bwd_colsum(da0, z0)
         dW0 = wgrad(dz0, xb) if need[1] else None
         dx = dgrad(dz0, W0) if need[0] else None
+        if dx is not None and dx.shape[0] != M:
+            dx = dx[:M]
         dts = ctx.dtypes
         cast = lambda g, dt: None if g is None else g.to(dt)  # noqa: E731
         return (cast(dx, dts[0]), cast(dW0, dts[1]), cast(db0, dts[2]) if need[2] else None, cast(dW2, dts[3]),

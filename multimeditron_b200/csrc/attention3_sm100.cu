@@ -583,13 +583,13 @@ int launch_attention3(const void* qkv, void* out, int B, int T, int heads, float
   if (rc != MM_OK) return rc;
   rc = make_tmap_3d(&maps.kv, qkv, W, T, B, W, (int64_t)T * W, BKV);
   if (rc != MM_OK) return rc;
-  static bool attr_set[64] = {false};
+  static std::atomic<bool> attr_set[64];
   int dev = 0;
   MM_CUDA_CHECK(cudaGetDevice(&dev));
-  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+  if (dev >= 0 && dev < 64 && !attr_set[dev].load(std::memory_order_acquire)) {
     MM_CUDA_CHECK(cudaFuncSetAttribute(attention3_fwd_kernel<BKV, NSTR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        C::kSmemBytes));
-    attr_set[dev] = true;
+    attr_set[dev].store(true, std::memory_order_release);
   }
   const int units = B * heads;
   const int sms = sm_count();

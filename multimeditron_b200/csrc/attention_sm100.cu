@@ -711,13 +711,13 @@ static int launch_attention(const void* qkv, const AttnParams& p, cudaStream_t s
     maps.q_x = maps.q_main;
     maps.kv_x = maps.kv_main;
   }
-  static bool attr_set[64] = {false};
+  static std::atomic<bool> attr_set[64];
   int dev = 0;
   MM_CUDA_CHECK(cudaGetDevice(&dev));
-  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+  if (dev >= 0 && dev < 64 && !attr_set[dev].load(std::memory_order_acquire)) {
     MM_CUDA_CHECK(cudaFuncSetAttribute(attention_fwd_kernel<HD, BKV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        Cfg::kSmemBytes));
-    attr_set[dev] = true;
+    attr_set[dev].store(true, std::memory_order_release);
   }
   const int units = p.B * p.heads;
   const int sms = sm_count();

@@ -2,6 +2,7 @@
 // Hand-written inline PTX; encodings cross-checked against the PTX ISA tables that the
 // vendored CUTLASS headers (cute/arch/mma_sm100_desc.hpp) restate.
 #pragma once
+#include <atomic>
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>

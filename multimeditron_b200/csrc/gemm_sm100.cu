@@ -648,13 +648,13 @@ int make_tmap_3d_sw32(CUtensorMap* tm, const void* ptr, int64_t d0, int64_t d1, 
 template <bool kGatherA, int ACT, int LN, bool kPair>
 static int launch_gemm_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
   using Cfg = GemmCfg<kGatherA, kPair>;
-  static bool attr_set[64] = {false};
+  static std::atomic<bool> attr_set[64];   // per device, set once (idempotent call; atomics make the race benign)
   int dev = 0;
   MM_CUDA_CHECK(cudaGetDevice(&dev));
   auto* kern = gemm_bf16_tn_kernel<kGatherA, ACT, LN, kPair>;
-  if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+  if (dev >= 0 && dev < 64 && !attr_set[dev].load(std::memory_order_acquire)) {
     MM_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    attr_set[dev] = true;
+    attr_set[dev].store(true, std::memory_order_release);
   }
   constexpr int kTileRows = kPair ? 2 * BM : BM;
   p.tiles_m = (p.M + kTileRows - 1) / kTileRows;
@@ -673,11 +673,10 @@ static int launch_gemm_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmP
   return MM_OK;
 }
 
-// CTA-pair kernel on/off: mm_set_gemm_pair(), else the environment (MM_B200_GEMM_PAIR=0 forces the 1-CTA kernel
-// everywhere — A/B measurements and the pair-vs-single parity test), else on.
-static int g_pair_override = -1;
+// CTA-pair kernel on/off: per call through MM_GEMM_FLAG_1CTA in the `act` argument (the pair-vs-single parity test),
+// else the environment read ONCE (MM_B200_GEMM_PAIR=0 forces the 1-CTA kernel everywhere for A/B measurements), else
+// on.  No mutable process state: concurrent launches from several threads / streams never see each other's choice.
 static bool pair_enabled() {
-  if (g_pair_override >= 0) return g_pair_override != 0;
   static const bool on = [] {
     const char* e = getenv("MM_B200_GEMM_PAIR");
     return !(e && e[0] == '0');
@@ -737,12 +736,14 @@ static int gemm_entry(const void* A, int64_t lda, const void* W, int64_t ldw, co
   if (lda < K || ldw < K || ldc < N) return MM_ERR_BAD_ARG;
   if (!aligned16(A) || !aligned16(W) || !aligned16(C) || !aligned16(bias) || !aligned16(residual))
     return MM_ERR_BAD_ARG;
+  const bool force_1cta = (act & MM_GEMM_FLAG_1CTA) != 0;
+  act &= ~MM_GEMM_FLAG_1CTA;
   if (act < MM_ACT_NONE || act > MM_ACT_GELU_TANH) return MM_ERR_BAD_ARG;
   if (out_row_map && n_out_rows <= 0) return MM_ERR_BAD_ARG;
   CUtensorMap tmA, tmB;
   int rc = make_tmap_2d(&tmA, A, M, K, lda, BM);
   if (rc != MM_OK) return rc;
-  const bool pair = M > BM && pair_enabled();   // at most one row tile: the peer CTA would only see padding
+  const bool pair = M > BM && !force_1cta && pair_enabled();   // at most one row tile: the peer CTA would only see padding
   rc = make_tmap_2d(&tmB, W, N, K, ldw, pair ? BN / 2 : BN);
   if (rc != MM_OK) return rc;
   GemmParams p{};
@@ -775,8 +776,6 @@ extern "C" int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64
   return gemm_entry(A, lda, W, ldw, bias, C, ldc, M, N, K, act, residual, ldr, res_mod, res_row_off, out_row_map,
                     n_out_rows, nullptr, nullptr, 0.f, stream);
 }
-
-extern "C" void mm_set_gemm_pair(int on) { g_pair_override = on < 0 ? -1 : (on ? 1 : 0); }
 
 extern "C" int64_t mm_gemm_row_stats_slots(int64_t N) { return (N > 0 && N <= 128 * kStatSlots) ? kStatSlots : -1; }
 

@@ -5,16 +5,16 @@ namespace mm {
 thread_local int g_last_cuda_error = 0;
 
 int sm_count() {
-  static int cached[64] = {0};
+  static std::atomic<int> cached[64];
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return 148;
   if (dev < 0 || dev >= 64) return 148;
-  if (cached[dev] == 0) {
+  if (cached[dev].load(std::memory_order_acquire) == 0) {
     int n = 0;
     if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
-    cached[dev] = n;
+    cached[dev].store(n, std::memory_order_release);
   }
-  return cached[dev];
+  return cached[dev].load(std::memory_order_acquire);
 }
 }  // namespace mm
 

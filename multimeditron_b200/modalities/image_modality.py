@@ -130,8 +130,16 @@ class B200ImageModality(BaseModality):
 
     # -- the plugin call ----------------------------------------------------------------------------------------
     def _preprocessor(self) -> DevicePreprocessor:
+        """Device resize/crop/normalise.  A checkpoint directory carries its own `preprocessor_config.json`: the device
+        path is built from THAT (mean/std, sizes, resample ...; unsupported settings raise).  Only the named synthetic
+        towers of configs.TOWERS (no checkpoint, no processor file) use the architecture's stock defaults."""
         if self._pre is None:
-            self._pre = DevicePreprocessor.for_tower(self.tower)
+            name = self.config.clip_name
+            if isinstance(name, str) and name not in TOWERS:
+                from transformers import AutoImageProcessor
+                self._pre = DevicePreprocessor.from_hf_processor(AutoImageProcessor.from_pretrained(name), self.tower)
+            else:
+                self._pre = DevicePreprocessor.for_tower(self.tower)
             self._pre.uploader = self._uploader()
         return self._pre
 

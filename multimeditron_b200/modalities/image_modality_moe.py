@@ -21,7 +21,7 @@ from typing import Any, Callable, Dict, List, Optional, Sequence
 import torch
 
 from .. import ops
-from ..configs import TowerConfig
+from ..configs import TOWERS, TowerConfig
 from ..h2d import H2DUploader
 from ..preprocess import DevicePreprocessor, PackedImages
 from ..vit import ProjectorWeights, TowerRunner, TowerWeights
@@ -184,7 +184,12 @@ class _B200MOEBase(BaseModality):
             # raw uint8 images (mixed resolutions): resize / crop / normalise on the device, bit-exact with the
             # experts' shared HF image processor (image_modality_moe.py:96-99 of the reference)
             if self._pre is None:
-                self._pre = DevicePreprocessor.for_tower(self.towers[0])
+                ipn = getattr(self.config, "image_processor", None)
+                if isinstance(ipn, str) and ipn not in TOWERS:    # a checkpoint directory: use ITS preprocessor_config
+                    from transformers import AutoImageProcessor
+                    self._pre = DevicePreprocessor.from_hf_processor(AutoImageProcessor.from_pretrained(ipn), self.towers[0])
+                else:
+                    self._pre = DevicePreprocessor.for_tower(self.towers[0])
                 self._pre.uploader = H2DUploader(self._device)     # host bytes travel on a copy stream
             return self._pre(inputs, self._device, torch.bfloat16)
         if torch.is_tensor(inputs):
@@ -243,6 +248,38 @@ class _B200MOEBase(BaseModality):
         if self._pre is not None and self._pre.uploader is not None:
             self._pre.uploader.release()
 
+    def _each_expert(self, fn):
+        """Run fn(e, runner) for every expert, expert e on its own CUDA stream (fork from / join into the current
+        stream).  Each expert's GEMMs are persistent kernels with a short tail wave (cfg5: 150 tiles on 74 CTA pairs =
+        2.03 waves); side by side, expert e+1's CTAs start on the SMs expert e's tail leaves idle, and the gating network
+        (current stream) overlaps the experts.  MM_B200_MOE_STREAMS=0 serialises them on the current stream (A/B)."""
+        import os
+        if os.environ.get("MM_B200_MOE_STREAMS", "1") == "0" or len(self._runners) == 1:
+            for e, r in enumerate(self._runners):
+                fn(e, r)
+            return
+        cur = torch.cuda.current_stream(self._device)
+        if getattr(self, "_streams", None) is None or len(self._streams) != len(self._runners):
+            self._streams = [torch.cuda.Stream(device=self._device) for _ in self._runners]
+        fork = torch.cuda.Event()
+        fork.record(cur)
+        joins = []
+        for e, r in enumerate(self._runners):
+            st = self._streams[e]
+            st.wait_event(fork)
+            with torch.cuda.stream(st):
+                fn(e, r)
+                ev = torch.cuda.Event()
+                ev.record(st)
+                joins.append(ev)
+        self._joins = joins
+
+    def _join_experts(self):
+        cur = torch.cuda.current_stream(self._device)
+        for ev in getattr(self, "_joins", None) or []:
+            cur.wait_event(ev)
+        self._joins = None
+
     def _run(self, px: torch.Tensor, out2d: torch.Tensor, dest_rows: Optional[torch.Tensor]):
         raise NotImplementedError
 
@@ -269,15 +306,16 @@ class B200MOEImageModality(_B200MOEBase):
         D = self._native_embed_dim
         r0, proj = self._runners[0], self._projs[0]
         if self.fusion_method == "weighted_average":
-            w = self._weights(px)                                                  # :156
             stack = torch.empty(E, B * P, D, dtype=torch.bfloat16, device=self._device)
-            for e, r in enumerate(self._runners):                                  # :160-162 (every expert)
-                r.features(px, out=stack[e])
+            self._each_expert(lambda e, r: r.features(px, out=stack[e]))           # :160-162 (every expert)
+            w = self._weights(px)                                                  # :156 (overlaps the experts)
+            self._join_experts()
             fused = ops.weighted_expert_sum(stack, w, self._perm, B, P)            # :171-177 (permuted weights)
         else:                                                                      # sequence_append :167-169
             fused = torch.empty(B * E * P, D, dtype=torch.bfloat16, device=self._device)
-            for e, r in enumerate(self._runners):
-                r.features(px, out=fused, out_row_map=self._append_map(B, e))
+            maps = [self._append_map(B, e) for e in range(E)]
+            self._each_expert(lambda e, r: r.features(px, out=fused, out_row_map=maps[e]))
+            self._join_experts()
         r0.project(fused, proj, out=out2d, out_row_map=dest_rows)                  # :207
 
 
@@ -291,18 +329,19 @@ class B200MOEImageModalityPEP(_B200MOEBase):
     def _run(self, px, out2d, dest_rows):
         B, E, P, H = px.shape[0], len(self.towers), self._num_patches_per_entry, self.config.hidden_size
         if self.fusion_method == "weighted_average":
-            w = self._weights(px)                                                  # :194
             stack = torch.empty(E, B * P, H, dtype=torch.bfloat16, device=self._device)
-            for e, (r, pw) in enumerate(zip(self._runners, self._projs)):          # :198-203
-                r.project(r.features(px), pw, out=stack[e])
+            self._each_expert(lambda e, r: r.project(r.features(px), self._projs[e], out=stack[e]))   # :198-203
+            w = self._weights(px)                                                  # :194 (overlaps the experts)
+            self._join_experts()
             fused = ops.weighted_expert_sum(stack, w, None, B, P)                  # :212-216 (NO permutation)
             if dest_rows is None:
                 out2d.copy_(fused)
             else:
                 ops.splice_scatter(out2d, fused, dest_rows)
         else:                                                                      # sequence_append :206-209
-            for e, (r, pw) in enumerate(zip(self._runners, self._projs)):
+            maps = []
+            for e in range(E):
                 m = self._append_map(B, e)
-                if dest_rows is not None:
-                    m = dest_rows[m.long()].contiguous()
-                r.project(r.features(px), pw, out=out2d, out_row_map=m)
+                maps.append(m if dest_rows is None else dest_rows[m.long()].contiguous())
+            self._each_expert(lambda e, r: r.project(r.features(px), self._projs[e], out=out2d, out_row_map=maps[e]))
+            self._join_experts()

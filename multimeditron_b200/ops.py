@@ -297,9 +297,7 @@ def gemm_ln_bias_act(a: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None
     return out
 
 
-def set_gemm_pair(on: int) -> None:
-    """0: 1-CTA GEMM kernel, 1: CTA-pair (cta_group::2) kernel, -1: default (pair for M > 128).  Results are bit-identical."""
-    _lib.load().mm_set_gemm_pair(int(on))
+GEMM_FLAG_1CTA = 0x100   # per-call: OR into `act` to run the 1-CTA kernel instead of the CTA pair (bit-identical results)
 
 
 def row_stats_slots(n: int) -> int:
@@ -325,7 +323,7 @@ def fold_layernorm(w: torch.Tensor, bias: torch.Tensor | None, gamma: torch.Tens
     return q, bo
 
 
-_patch_ws: dict = {}   # device -> scratch for the staged patch rows (grown on demand, reused across calls)
+_patch_ws: dict = {}   # (device, stream) -> scratch for the staged patch rows (grown on demand, reused across calls)
 
 
 def patch_embed(pixels: torch.Tensor, weight_padded: torch.Tensor, conv_bias, pos_emb: torch.Tensor, cls,
@@ -345,9 +343,10 @@ def patch_embed(pixels: torch.Tensor, weight_padded: torch.Tensor, conv_bias, po
             global LAUNCHES
             LAUNCHES += 1   # patch_rows_kernel (the context manager counts the GEMM and the CLS kernel)
             need = int(lib.mm_patch_embed_workspace_bytes(B, img, patch))
-            ws = _patch_ws.get(pixels.device)
+            key = (pixels.device, _stream())     # one scratch per (device, stream): concurrent streams never share it
+            ws = _patch_ws.get(key)
             if ws is None or ws.numel() < need:
-                ws = _patch_ws[pixels.device] = torch.empty(need, dtype=torch.uint8, device=pixels.device)
+                ws = _patch_ws[key] = torch.empty(need, dtype=torch.uint8, device=pixels.device)
             rc = lib.mm_patch_embed_ws(_ptr(pixels), _dt(pixels), B, img, patch, _ptr(weight_padded),
                                        weight_padded.stride(0), _ptr(conv_bias), _ptr(pos_emb), _ptr(cls), _ptr(out), D,
                                        _ptr(ws), ws.numel(), _stream())

@@ -110,6 +110,59 @@ class DevicePreprocessor:
             return cls(tower.image_size, (0.5, 0.5, 0.5), (0.5, 0.5, 0.5), square=True)
         return cls(tower.image_size)
 
+    @classmethod
+    def from_hf_processor(cls, ip, tower=None) -> "DevicePreprocessor":
+        """Build from the checkpoint's HF image processor (`preprocessor_config.json`), so that the device path
+        reproduces exactly what `ImageProcessor.process` (image_modality.py:96) would have produced on the CPU for THIS
+        checkpoint.  Every setting the kernels do not implement raises instead of silently falling back to the
+        OpenAI-CLIP defaults: resample != bicubic, do_resize/do_rescale/do_normalize off, non-square crops, a crop size
+        different from the resize target (CLIP) or any crop at all for the square-resize processors (SigLIP), padding."""
+        def get(name, default=None):
+            return getattr(ip, name, default)
+
+        def side(d, what):
+            if d is None:
+                return None
+            if isinstance(d, int):
+                return ("edge", int(d))
+            d = dict(d)
+            if "shortest_edge" in d and len(d) == 1:
+                return ("edge", int(d["shortest_edge"]))
+            if "height" in d and "width" in d:
+                if int(d["height"]) != int(d["width"]):
+                    raise ValueError(f"device preprocessing needs a square {what}, got {d}")
+                return ("square", int(d["height"]))
+            raise ValueError(f"unsupported {what} specification {d}")
+
+        for flag in ("do_resize", "do_rescale", "do_normalize"):
+            if get(flag, True) is False:
+                raise ValueError(f"device preprocessing does not implement {flag}=False (image processor {type(ip).__name__})")
+        if get("do_pad", False):
+            raise ValueError("device preprocessing does not implement do_pad=True")
+        rs = get("resample", 3)
+        rs = int(getattr(rs, "value", rs)) if rs is not None else 3
+        if rs != 3:      # PIL.Image.Resampling.BICUBIC == 3
+            raise ValueError(f"device preprocessing implements bicubic resampling only (resample={rs})")
+        size = side(get("size"), "size")
+        if size is None:
+            raise ValueError("image processor has no `size`")
+        crop = side(get("crop_size"), "crop_size") if get("do_center_crop", False) else None
+        if size[0] == "edge":          # CLIP style: shortest edge -> S, then center crop S x S
+            if crop is None or crop[1] != size[1]:
+                raise ValueError(f"shortest-edge resize needs a center crop of the same size (size={size[1]}, crop={crop})")
+            square, out = False, size[1]
+        else:                          # SigLIP style: resize to (S, S), no crop
+            if crop is not None and crop[1] != size[1]:
+                raise ValueError(f"square resize followed by a different center crop is not implemented (size={size[1]}, crop={crop[1]})")
+            square, out = True, size[1]
+        if tower is not None and out != tower.image_size:
+            raise ValueError(f"image processor produces {out}px images, the tower expects {tower.image_size}px")
+        mean, std = get("image_mean"), get("image_std")
+        if mean is None or std is None or len(mean) != 3 or len(std) != 3:
+            raise ValueError("image processor needs 3-channel image_mean / image_std")
+        return cls(out, tuple(float(m) for m in mean), tuple(float(v) for v in std), square=square,
+                   rescale_factor=float(get("rescale_factor", 1 / 255)))
+
     def _batched(self, images: torch.Tensor, device, out_dtype) -> torch.Tensor:
         """One uint8 [B,H,W,3] tensor (same-size images, e.g. a pinned host batch): no packing copy — the tensor itself
         is the source buffer, only the small descriptor table is staged."""

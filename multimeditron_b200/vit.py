@@ -119,7 +119,9 @@ class TowerRunner:
 
     # -- workspaces ----------------------------------------------------------------------------------------
     def _workspace(self, B: int):
-        ws = self._ws.get(B)
+        # keyed by (batch, CUDA stream): two streams driving the same runner get separate activation buffers
+        key = (B, torch.cuda.current_stream(self.w.device).cuda_stream)
+        ws = self._ws.get(key)
         if ws is None:
             c, dev = self.cfg, self.w.device
             M, D, I = B * c.num_tokens, c.hidden_size, c.intermediate_size
@@ -130,8 +132,9 @@ class TowerRunner:
                 t = m % c.num_tokens
                 ws["drop_cls"] = torch.where(t == 0, torch.full_like(m, -1),
                                              (m // c.num_tokens) * c.num_patches + t - 1).to(torch.int32)
-            self._ws.clear()    # keep only the latest batch size resident
-            self._ws[B] = ws
+            for k in [k for k in self._ws if k[1] == key[1]]:
+                del self._ws[k]   # keep only the latest batch size resident per stream
+            self._ws[key] = ws
         return ws
 
     # -- tower -----------------------------------------------------------------------------------------------
@@ -195,13 +198,16 @@ class TowerRunner:
 
     @staticmethod
     def _compose(ws, out_row_map: torch.Tensor) -> torch.Tensor:
-        """token-row map = out_row_map[drop_cls[m]] (with -1 kept); cached per map tensor."""
+        """token-row map = out_row_map[drop_cls[m]] (with -1 kept); cached per map TENSOR: the cache entry keeps the map
+        alive (so its address cannot be handed to another tensor while the entry exists) and records its version
+        counter (an in-place edit of the map invalidates the entry)."""
         key = ("compose", out_row_map.data_ptr(), out_row_map.numel())
-        m = ws.get(key)
-        if m is None:
-            dc = ws["drop_cls"].long()
-            m = torch.where(dc >= 0, out_row_map.long()[dc.clamp(min=0)], dc).to(torch.int32)
-            ws[key] = m
+        hit = ws.get(key)
+        if hit is not None and hit[0] is out_row_map and hit[1] == out_row_map._version:
+            return hit[2]
+        dc = ws["drop_cls"].long()
+        m = torch.where(dc >= 0, out_row_map.long()[dc.clamp(min=0)], dc).to(torch.int32)
+        ws[key] = (out_row_map, out_row_map._version, m)
         return m
 
     # -- projector ---------------------------------------------------------------------------------------------

@@ -160,20 +160,17 @@ def test_gemm_pair_kernel_bit_identical_to_single_cta(M, N, K):
     wf, bf = ops.fold_layernorm(w, bs, gamma, beta)
     ln_stats = (torch.rand(M, 16, 2, generator=g0) * 64 + 0.5).to(DEV)
     got = {}
-    try:
-        for pair in (0, 1):
-            ops.set_gemm_pair(pair)
-            o_map = torch.full((M, N), 7.0, device=DEV).bfloat16()
-            ops.gemm_bias_act(a, w, bs, 2, residual=res, out=o_map, out_row_map=perm)
-            outs = [ops.gemm_bias_act(a, w, None), ops.gemm_bias_act(a, w, bs, 1), o_map]
-            if N <= 2048:
-                st = torch.zeros(M, 16, 2, device=DEV)
-                outs += [ops.gemm_ln_bias_act(a, w, bs, residual=res, stats_out=st), st]
-            if K <= 2048:
-                outs.append(ops.gemm_ln_bias_act(a, wf, bf, act=1, ln_stats=ln_stats, eps=1e-5))
-            got[pair] = outs
-    finally:
-        ops.set_gemm_pair(-1)
+    for pair in (0, 1):
+        f = 0 if pair else ops.GEMM_FLAG_1CTA      # per-call flag in `act` (no process-wide switch)
+        o_map = torch.full((M, N), 7.0, device=DEV).bfloat16()
+        ops.gemm_bias_act(a, w, bs, 2 | f, residual=res, out=o_map, out_row_map=perm)
+        outs = [ops.gemm_bias_act(a, w, None, f), ops.gemm_bias_act(a, w, bs, 1 | f), o_map]
+        if N <= 2048:
+            st = torch.zeros(M, 16, 2, device=DEV)
+            outs += [ops.gemm_ln_bias_act(a, w, bs, act=f, residual=res, stats_out=st), st]
+        if K <= 2048:
+            outs.append(ops.gemm_ln_bias_act(a, wf, bf, act=1 | f, ln_stats=ln_stats, eps=1e-5))
+        got[pair] = outs
     for x, y in zip(got[0], got[1]):
         assert torch.equal(x, y)
     close(got[1][0], a.float() @ w.float().t())

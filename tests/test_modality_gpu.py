@@ -158,3 +158,39 @@ def test_full_size_cfg2_batch_independence_and_splice_placement():
     assert int(is_att.sum()) == B * P
     assert torch.equal(flat[is_att], y.view(B * P, H))               # row-major order == collator order (model.py:443-444)
     assert torch.equal(flat[~is_att], table[idsd[~is_att]])          # text rows untouched, bit-exact
+
+
+def test_two_streams_and_two_host_threads_share_one_modality():
+    """B4 / include/mm_b200.h: re-entrant across streams and host threads.  One modality instance is driven from two
+    CUDA streams at once (launches interleaved by two Python threads, each with its own stream): per-stream activation
+    workspaces and patch scratch, no process-wide switches — every result must equal the sequential single-stream one."""
+    import threading
+    cfg = TOWERS["clip_b32"]
+    m, _ = _modality("clip_b32", 512, 11)
+    batches = [synth.make_pixels(cfg, 6, seed=20 + i).to(DEV) for i in range(4)]
+    want = [m(b).clone() for b in batches]
+    torch.cuda.synchronize()
+    got, errs = [None] * 4, []
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    start = threading.Barrier(2)
+
+    def worker(t):
+        try:
+            with torch.cuda.stream(streams[t]):
+                start.wait()
+                for rep in range(3):
+                    for i in (t, t + 2):
+                        got[i] = m(batches[i]).clone()
+            streams[t].synchronize()
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    for s in streams:
+        s.wait_stream(torch.cuda.current_stream())
+    ths = [threading.Thread(target=worker, args=(t,)) for t in range(2)]
+    [t.start() for t in ths]
+    [t.join() for t in ths]
+    torch.cuda.synchronize()
+    assert not errs, errs
+    for i in range(4):
+        assert torch.equal(got[i], want[i]), f"batch {i} differs when two streams run concurrently"

@@ -68,3 +68,34 @@ def test_fused_mean_std_matches_hf_fusion():
     p = pre.DevicePreprocessor(224)
     m, s = po.fused_mean_std(po.OPENAI_CLIP_MEAN, po.OPENAI_CLIP_STD)
     assert np.array_equal(np.asarray(p.mean255, np.float32), m) and np.array_equal(np.asarray(p.std255, np.float32), s)
+
+
+def test_device_preprocessor_follows_the_checkpoints_image_processor():
+    """the device path must take mean/std, sizes, crop and resample from the checkpoint's HF image
+    processor instead of assuming the OpenAI-CLIP defaults, and refuse what the kernels do not implement."""
+    tr = pytest.importorskip("transformers")
+    from multimeditron_b200.configs import TOWERS
+    ip = tr.CLIPImageProcessor(size={"shortest_edge": 336}, crop_size={"height": 336, "width": 336},
+                               image_mean=[0.1, 0.2, 0.3], image_std=[0.4, 0.5, 0.6])
+    p = pre.DevicePreprocessor.from_hf_processor(ip, TOWERS["clip_l14_336"])
+    m, s = po.fused_mean_std((0.1, 0.2, 0.3), (0.4, 0.5, 0.6))
+    assert p.size == 336 and p.square is False
+    assert np.array_equal(np.asarray(p.mean255, np.float32), m) and np.array_equal(np.asarray(p.std255, np.float32), s)
+    sg = tr.SiglipImageProcessor(size={"height": 384, "width": 384})
+    q = pre.DevicePreprocessor.from_hf_processor(sg, TOWERS["siglip_so400m_384"])
+    assert q.size == 384 and q.square is True and np.allclose(q.mean255, [127.5] * 3)
+    # the stock processors give exactly what for_tower assumes for the named synthetic towers
+    d = pre.DevicePreprocessor.from_hf_processor(tr.CLIPImageProcessor(), TOWERS["clip_b32"])
+    f = pre.DevicePreprocessor.for_tower(TOWERS["clip_b32"])
+    assert (d.size, d.square, d.mean255, d.std255) == (f.size, f.square, f.mean255, f.std255)
+    with pytest.raises(ValueError):   # wrong output size for the tower
+        pre.DevicePreprocessor.from_hf_processor(tr.CLIPImageProcessor(), TOWERS["clip_l14_336"])
+    with pytest.raises(ValueError):   # bilinear resampling is not implemented
+        pre.DevicePreprocessor.from_hf_processor(tr.CLIPImageProcessor(resample=2), TOWERS["clip_b32"])
+    with pytest.raises(ValueError):   # crop size != resize target
+        pre.DevicePreprocessor.from_hf_processor(
+            tr.CLIPImageProcessor(size={"shortest_edge": 256}, crop_size={"height": 224, "width": 224}), TOWERS["clip_b32"])
+    with pytest.raises(ValueError):   # no normalisation
+        pre.DevicePreprocessor.from_hf_processor(tr.CLIPImageProcessor(do_normalize=False), TOWERS["clip_b32"])
+    with pytest.raises(ValueError):   # no center crop after a shortest-edge resize
+        pre.DevicePreprocessor.from_hf_processor(tr.CLIPImageProcessor(do_center_crop=False), TOWERS["clip_b32"])
