@@ -355,8 +355,12 @@ def run_b200(args):
             "expert_towers": {n: tower for n in names}, "image_processor": tower, "fusion_method": "weighted_average",
             "top_k_experts": 1, "gating_class_names": [names[i] for i in order]})
         sd = synth.make_moe_state_dict([cfg] * E, H, False, seed=0, dtype=torch.bfloat16)
-        gate_w = torch.softmax(torch.randn(images, E, generator=torch.Generator().manual_seed(7 + rank)), -1).to(dev)
-        modality, model_load_s = timed_load(AutoModality.from_config(mcfg), sd, dev, gating=lambda _px: gate_w)
+        # the reference's gate ON the path (moe/gating.py:73-89: ResNet-50 -> logits -> softmax), random init like the
+        # experts; torchvision/cuDNN (library code: SURVEY §8(f) rank 3 keeps it there), bf16 channels-last
+        from multimeditron_b200.gating import ResNet50Gate
+        torch.manual_seed(7)
+        gate = ResNet50Gate(E, top_k=1, device=dev)
+        modality, model_load_s = timed_load(AutoModality.from_config(mcfg), sd, dev, gating=gate)
         # raw mixed-resolution images, packed once (what the collator would hand over), resized on the device
         from multimeditron_b200.preprocess import DevicePreprocessor
         g = torch.Generator().manual_seed(400 + rank)
@@ -475,6 +479,13 @@ def run_b200(args):
     splice_bytes = 2.0 * images * P * H * 2
     del proj, emb
 
+    gate_ms = None
+    if E:
+        gpx = torch.randn(images, 3, cfg.image_size, cfg.image_size, device=dev).bfloat16()
+        for _ in range(2):
+            gate(gpx)
+        gate_ms = timed(lambda: gate(gpx), max(5, args.steps))
+        del gpx
     total_images = images * world
     pk = peaks()
     flops_img = cfg.flops_per_image(H)
@@ -534,7 +545,11 @@ def run_b200(args):
     if E:
         line["config"]["experts"] = E
         line["config"]["inputs"] = "raw uint8 images, sizes drawn from {224,336,512,1024}^2, resized on the device"
-        line["config"]["gating"] = "synthetic softmax weights (ResNet-50 gate not on the path, SURVEY §8(f) rank 3)"
+        line["config"]["gating"] = ("reference GatingNetwork on the path: torchvision ResNet-50 (cuDNN, bf16 channels-last) on every "
+                                    "image inside the timed step, overlapping the experts' streams; its FLOPs (~8.2 GFLOP/img) "
+                                    "are NOT credited in path_tensor")
+        line["config"]["expert_streams"] = os.environ.get("MM_B200_MOE_STREAMS", "1") != "0"
+        line["gate_ms_standalone"] = gate_ms
     if rank == 0 and world == 1 and not args.no_cpu_baseline and not E:
         threads = os.cpu_count() or 1
         line["cpu_baseline"] = cpu_baseline_block(args.workload, args.cpu_sample, threads, budget_s=12.0)

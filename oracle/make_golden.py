@@ -324,6 +324,9 @@ MOE_CASES = [  # name, per-expert projector, fusion, experts, hidden, batch, wei
     ("moe_shared_append", False, "sequence_append", 3, 64, 2, 22, 6),
     ("moe_pep_avg", True, "weighted_average", 3, 64, 3, 23, 7),
     ("moe_pep_append", True, "sequence_append", 3, 64, 2, 24, 8),
+    # CLIP ViT-B/32-sized experts (the cfg5 expert shape: D 768, 12 layers, 12 heads, T = 50) -> hidden 512
+    ("moe_shared_avg_b32", False, "weighted_average", 3, 512, 2, 31, 9, "clip_b32"),
+    ("moe_pep_avg_b32", True, "weighted_average", 3, 512, 2, 33, 10, "clip_b32"),
 ]
 MOE_CLASS_ORDER = [2, 0, 1]   # gating class c is expert MOE_CLASS_ORDER[c]  (non-identity on purpose)
 
@@ -349,8 +352,13 @@ def gen_moe(ref):
     from multimeditron.model.modalities.image_modality_moe import MOEImageConfig, MOEImageModality
     from multimeditron.model.modalities.image_modality_moe_pep import MOEImageConfigPEP, MOEImageModalityPEP
     from multimeditron.model.modalities.moe.gating import GatingNetwork, GatingNetworkConfig
-    cfg = TOWERS["tiny"]
-    for name, pep, fusion, E, hidden, batch, wseed, pseed in MOE_CASES:
+    only = os.environ.get("MOE_ONLY")
+    for case in MOE_CASES:
+        name, pep, fusion, E, hidden, batch, wseed, pseed = case[:8]
+        tower = case[8] if len(case) > 8 else "tiny"
+        if only and only not in name:
+            continue
+        cfg = TOWERS[tower]
         dirs = [save_tiny_clip(cfg) for _ in range(E)]
         gdir = tempfile.mkdtemp(prefix="gating_")
         torch.manual_seed(wseed)
@@ -387,7 +395,7 @@ def gen_moe(ref):
         print(f"[{name}] out {tuple(y32.shape)} absmax {y32.abs().max():.4f} bf16-vs-fp32 maxabs {err:.3e} "
               f"weights {w32[0].tolist()}")
         np.savez_compressed(os.path.join(GOLD, f"{name}.npz"), pep=pep, fusion=fusion, experts=E, hidden=hidden,
-                            batch=batch, wseed=wseed, pseed=pseed, perm=np.array(perm), weights32=w32.numpy(),
+                            batch=batch, wseed=wseed, pseed=pseed, perm=np.array(perm), weights32=w32.numpy(), tower=tower,
                             out_fp32=y32.numpy(), out_bf16_w32_bits=bf16_bits(ob_w32))
 
 

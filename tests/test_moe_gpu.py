@@ -15,17 +15,19 @@ from oracle import splice_oracle
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
-MOE_NAMES = ["moe_shared_avg", "moe_shared_append", "moe_pep_avg", "moe_pep_append"]
+MOE_NAMES = ["moe_shared_avg", "moe_shared_append", "moe_pep_avg", "moe_pep_append",
+             "moe_shared_avg_b32", "moe_pep_avg_b32"]       # *_b32: CLIP ViT-B/32-sized experts (the cfg5 expert shape)
 
 
 def _build(g):
-    cfg = TOWERS["tiny"]
+    tower = str(g["tower"]) if "tower" in g.files else "tiny"
+    cfg = TOWERS[tower]
     E, hidden, pep = int(g["experts"]), int(g["hidden"]), bool(g["pep"])
     names = [f"expert{i}" for i in range(E)]
     perm = g["perm"].tolist()
     mcfg = AutoModality.config_from_dict({
         "model_type": "moe_meditron_clip_pep_b200" if pep else "moe_meditron_clip_b200", "hidden_size": hidden,
-        "expert_clip_names": names, "expert_towers": {n: "tiny" for n in names}, "image_processor": "tiny",
+        "expert_clip_names": names, "expert_towers": {n: tower for n in names}, "image_processor": tower,
         "fusion_method": str(g["fusion"]), "top_k_experts": E if str(g["fusion"]) == "sequence_append" else 1,
         "gating_class_names": [names[i] for i in perm]})
     sd = synth.make_moe_state_dict([cfg] * E, hidden, pep, seed=int(g["wseed"]))

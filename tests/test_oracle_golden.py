@@ -110,7 +110,7 @@ def test_c_oracle_agrees_with_numpy_oracle():
     assert np.array_equal(out, want)
 
 
-MOE_NAMES = ["moe_shared_avg", "moe_shared_append", "moe_pep_avg", "moe_pep_append"]
+MOE_NAMES = ["moe_shared_avg", "moe_shared_append", "moe_pep_avg", "moe_pep_append", "moe_shared_avg_b32", "moe_pep_avg_b32"]
 
 
 @pytest.mark.parametrize("name", MOE_NAMES)
@@ -118,7 +118,7 @@ def test_moe_oracle_matches_reference_golden(golden_dir, name):
     """MOEImageModality / MOEImageModalityPEP run by oracle/make_golden.py (all experts, gating-weighted fusion, the
     PEP 'no permutation' quirk with a non-identity class order)."""
     g = np.load(os.path.join(golden_dir, f"{name}.npz"))
-    cfg = TOWERS["tiny"]
+    cfg = TOWERS[str(g["tower"]) if "tower" in g.files else "tiny"]
     E, hidden, batch, pep = int(g["experts"]), int(g["hidden"]), int(g["batch"]), bool(g["pep"])
     sd = synth.make_moe_state_dict([cfg] * E, hidden, pep, seed=int(g["wseed"]))
     px = synth.make_pixels(cfg, batch, seed=int(g["pseed"]))
