@@ -337,6 +337,20 @@ def run_b200(args):
         images = args.images_per_gpu
     cfg, H, V, S, att, ids, px = build_inputs(args.workload, 100 + rank, images, torch, synth, TOWERS)
     P = cfg.num_patches
+    real_info = None
+    if args.real_images:
+        # real photographs through the REAL CPU image processor (what ImageProcessor.process runs,
+        # image_modality.py:96) -> fp32 pixel_values; the device pre-processor must reproduce them bit for bit
+        from transformers import CLIPImageProcessor
+        raws = synth.load_mock_images(images)
+        ip = CLIPImageProcessor(size={"shortest_edge": cfg.image_size},
+                                crop_size={"height": cfg.image_size, "width": cfg.image_size})
+        px = torch.stack([ip(images=r.numpy(), return_tensors="pt")["pixel_values"][0] for r in raws], 0).contiguous()
+        from multimeditron_b200.preprocess import DevicePreprocessor
+        dp = DevicePreprocessor.from_hf_processor(ip, cfg)(raws, torch.device("cuda", local_rank), torch.float32)
+        real_info = {"source": "tests/golden/mock (the reference's mock_dataset photographs, downscaled)",
+                     "sizes": sorted({tuple(r.shape[:2]) for r in raws}),
+                     "device_preprocess_bit_exact_vs_hf_cpu": bool(torch.equal(dp.cpu(), px))}
 
     # weights: replicated on every GPU (same seed), random init of the named architecture
     E = MOE_EXPERTS.get(args.workload, 0)
@@ -449,6 +463,31 @@ def run_b200(args):
     ms = timed(step_dev, args.steps)
     prof = ops.profile_stop()
     launches_per_step = ops.LAUNCHES // args.steps
+    # ---- optional: the same step replayed from ONE CUDA graph (launch-bound workloads: cfg1 is 132 launches for
+    # ~0.1 ms of math).  Captured after warm-up, so every one-time attribute / workspace allocation already happened;
+    # the graph's private pool keeps every pointer baked into a tensor map stable across replays.
+    graph_info = None
+    if args.cuda_graph:
+        ms_plain = timed(step_dev, args.steps)          # without the per-op event recording of the profiled region
+        gstream = torch.cuda.Stream(device=dev)
+        gstream.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(gstream):
+            for _ in range(2):
+                step_dev()                              # per-stream workspaces of the capture stream
+            gstream.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=gstream):
+                g_out = step_dev()
+        torch.cuda.current_stream(dev).wait_stream(gstream)
+        torch.cuda.synchronize()
+        ref_out = step_dev().clone()
+        graph.replay()
+        torch.cuda.synchronize()
+        same = bool(torch.equal(g_out, ref_out))
+        ms_graph = timed(graph.replay, max(args.steps, 20))
+        graph_info = {"ms_per_step": ms_graph, "value": images * world * P / (ms_graph * 1e-3),
+                      "ms_per_step_eager_no_profile": ms_plain, "replay_equals_eager": same,
+                      "note": "whole embed_modalities_with_text step captured once, replayed per step"}
     # ---- e2e region (host buffers)
     for _ in range(2):
         step_e2e()
@@ -499,7 +538,8 @@ def run_b200(args):
     line = {
         "metric": METRIC, "value": total_images * P / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
-        "dtype": "bf16", "data": "synthetic (seeded N(0,1) pixels, random-init weights; no network for checkpoints)",
+        "dtype": "bf16", "data": ("real photographs (mock_dataset) through the HF image processor, random-init weights" if args.real_images else
+                                  "synthetic (seeded N(0,1) pixels, random-init weights; no network for checkpoints)"),
         "config": {"workload": args.workload, "tower": tower, "llm_hidden": H, "images_per_gpu": images,
                    "global_images": total_images, "rows_per_gpu": ids.shape[0], "seq_len": S, "tokens_per_image": P, "parallelism": f"sample-shard x{world}",
                    "l2": "inputs larger than L2 (pixels %.0f MB, inputs_embeds %.0f MB per step)" % (
@@ -517,6 +557,8 @@ def run_b200(args):
         "e2e_prestacked": {"value": total_images * P / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                            "note": "same call, inputs handed over as ONE pre-stacked pinned host tensor (no host stack)"},
         "model_load_s": model_load_s,
+        "cuda_graph": graph_info,
+        "real_images": real_info,
         "e2e_uint8": {"value": total_images * P / (ms_e2e_u8 * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e_u8,
                       "h2d_bytes_per_step": int(raw_h.numel() + ids.numel() * 8), "d2h_bytes_per_step": int(H * 2 + 4),
                       "gpu_launches_per_step": launches_u8,
@@ -596,6 +638,9 @@ def main():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: images per GPU fixed; strong: the workload's GLOBAL batch split over the ranks")
     ap.add_argument("--cuda-graph", action="store_true", help="also time the step replayed from one CUDA graph")
+    ap.add_argument("--real-images", action="store_true",
+                    help="pixels = the reference's mock_dataset photographs (tests/golden/mock) through the HF image "
+                         "processor, cycled to the batch; the device pre-processor is checked bit-exact against it")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line: anything a library prints there (e.g. NCCL's version banner) goes to stderr

@@ -157,3 +157,20 @@ def make_raw_image(i: int, h: int, w: int):
         yy, xx = np.mgrid[0:h, 0:w]
         img = np.stack([(yy * 255 // max(1, h - 1)), (xx * 255 // max(1, w - 1)), ((yy + xx) % 256)], -1).astype(np.uint8)
     return img
+
+
+def load_mock_images(n: int):
+    """The two real photographs of the reference's `mock_dataset/` (cat.jpg 1200x1200, EPFL_campus_2017.jpg 2048x1365),
+    committed DOWNSCALED (Lanczos, lossless PNG) under tests/golden/mock/ because /root/reference does not travel to the
+    GPU box; cycled to `n` images ("cycle the 2 images to make batch 8").  -> list of uint8 [H,W,3] tensors."""
+    import glob
+    import os
+
+    import numpy as np
+    from PIL import Image
+    d = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "mock")
+    files = sorted(glob.glob(os.path.join(d, "*.png")))
+    if not files:
+        raise FileNotFoundError(f"no mock images under {d}")
+    imgs = [torch.from_numpy(np.array(Image.open(f).convert("RGB"), dtype=np.uint8)) for f in files]
+    return [imgs[i % len(imgs)] for i in range(n)]

@@ -68,3 +68,32 @@ def test_tower_and_projector_at_quoted_size(name, hidden, batch, massive):
     assert err <= 2.0 * ref_err
     assert err / scale <= 2e-2
     assert mean_rel <= 2.0 * ref_mean_rel
+
+
+@pytest.mark.parametrize("name,hidden,batch", [("clip_b32", 512, 8), ("clip_l14_336", 4096, 4)])
+def test_inference_regime_autocast(name, hidden, batch):
+    """SURVEY §8 C5 regime (ii): the regime the reference SHIPS for inference — bf16 weights under
+    `torch.autocast("cuda", torch.bfloat16)` (inference.py:36,88; ui/app.py:66-70,126).  There LayerNorm and softmax run
+    and RETURN fp32 (so the residual stream stays fp32) and Linear / conv re-cast to bf16.  The B200 path keeps the
+    pure-bf16 rounding points of regime (i); stated tolerance against regime (ii):
+        max|B200 - autocast| <= 2 x max|reference regime (i) - autocast|   and   <= 2e-2 of range,
+    i.e. switching a user from the reference's training regime to ours moves the inference result no more than the
+    reference's own two regimes differ."""
+    cfg = TOWERS[name]
+    sd = synth.make_modality_state_dict(cfg, hidden, seed=13)
+    px = synth.make_pixels(cfg, batch, seed=14)
+    m = AutoModality.from_config(AutoModality.config_from_dict(
+        {"model_type": "meditron_clip_b200", "hidden_size": hidden, "clip_name": name}))
+    m.load_reference_state_dict(sd, DEV)
+    y = m([px[i] for i in range(batch)]).float()
+    sdb = {k: v.to(DEV, torch.bfloat16) for k, v in sd.items()}
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        ref_ac = vit_oracle.image_modality_forward(sdb, cfg, px.to(DEV)).float()
+    ref_i = _oracle_gpu(sd, cfg, px, torch.bfloat16)          # regime (i): pure bf16 modules, no autocast
+    ref32 = _oracle_gpu(sd, cfg, px, torch.float32)
+    scale = ref_ac.abs().max().item()
+    err = (y - ref_ac).abs().max().item()
+    ref_err = (ref_i - ref_ac).abs().max().item()
+    print(f"[autocast {name} x{batch}] B200 vs regime (ii): max-abs {err:.3e} /absmax {err / scale:.3e}; reference regime (i) vs (ii): "
+          f"{ref_err:.3e}; regime (ii) vs fp32: {(ref_ac - ref32).abs().max().item():.3e}; B200 vs fp32: {(y - ref32).abs().max().item():.3e}")
+    assert err <= 2.0 * ref_err and err / scale <= 2e-2

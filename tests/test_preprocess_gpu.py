@@ -89,3 +89,19 @@ def test_batched_uint8_tensor_path_equals_list_path():
     a = p(raw, torch.device(DEV), torch.float32).cpu()
     for i in range(5):
         assert torch.equal(a[i], torch.from_numpy(po.clip_preprocess(raw[i].numpy(), 32)))
+
+
+@pytest.mark.parametrize("tower", ["clip_b32", "clip_l14_336"])
+def test_real_photographs_bit_exact_vs_hf_cpu_processor(tower):
+    """SURVEY D2 / VERDICT r1 #8: the reference's mock_dataset photographs (committed downscaled, tests/golden/mock)
+    through the REAL CPU image processor (what ImageProcessor.process runs, image_modality.py:96) vs the device path."""
+    tr = pytest.importorskip("transformers")
+    cfg = TOWERS[tower]
+    raws = synth.load_mock_images(4)
+    ip = tr.CLIPImageProcessor(size={"shortest_edge": cfg.image_size},
+                               crop_size={"height": cfg.image_size, "width": cfg.image_size})
+    want = torch.stack([ip(images=r.numpy(), return_tensors="pt")["pixel_values"][0] for r in raws], 0)
+    got = pre.DevicePreprocessor.from_hf_processor(ip, cfg)(raws, torch.device(DEV), torch.float32).cpu()
+    assert got.shape == want.shape == (4, 3, cfg.image_size, cfg.image_size)
+    assert torch.equal(got, want)
+    assert want.std().item() > 0.3          # real image content, not a constant

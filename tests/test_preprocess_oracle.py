@@ -99,3 +99,14 @@ def test_device_preprocessor_follows_the_checkpoints_image_processor():
         pre.DevicePreprocessor.from_hf_processor(tr.CLIPImageProcessor(do_normalize=False), TOWERS["clip_b32"])
     with pytest.raises(ValueError):   # no center crop after a shortest-edge resize
         pre.DevicePreprocessor.from_hf_processor(tr.CLIPImageProcessor(do_center_crop=False), TOWERS["clip_b32"])
+
+
+def test_oracle_bit_exact_on_the_real_mock_photographs():
+    """The numpy restatement vs the HF CPU processor on real pixels (the two mock_dataset photographs, downscaled)."""
+    tr = pytest.importorskip("transformers")
+    raws = synth.load_mock_images(2)
+    ip = tr.CLIPImageProcessor()     # shortest edge 224, center crop 224, OpenAI-CLIP mean/std
+    for r in raws:
+        want = ip(images=r.numpy(), return_tensors="pt")["pixel_values"][0].numpy()
+        got = po.clip_preprocess(r.numpy(), 224, po.OPENAI_CLIP_MEAN, po.OPENAI_CLIP_STD, square=False)
+        assert np.array_equal(got.view(np.int32), want.view(np.int32))
