@@ -254,6 +254,17 @@ int mm_weighted_expert_sum(const void* x, const float* w, const int32_t* perm, v
                            int64_t E, int64_t B, int64_t P, int64_t D, void* stream);
 
 /*
+ * mm_cross_attention — the MoE 'cross_attn' fusion's attention: generalist queries over the
+ * concatenated, gate-weighted specialist tokens.  Replaces src/multimeditron/model/attention.py:48-101
+ * (CrossAttention.forward between its q/k/v projections and its output projection; eval mode, no mask — the call sites
+ * image_modality_moe.py:205 and image_modality_moe_pep.py:245 pass none).
+ *   q [B, Nq, C] bf16; kv [B, Nkv, 2C] bf16 with columns [K | V] (one fused k_proj|v_proj GEMM); out [B, Nq, C] bf16;
+ *   head_dim = C / heads must be a multiple of 32 and <= 512; scale = head_dim**-0.5 (attention.py:33).
+ */
+int mm_cross_attention(const void* q, const void* kv, void* out, int64_t B, int64_t Nq, int64_t Nkv,
+                       int64_t heads, int64_t C, float scale, void* stream);
+
+/*
  * mm_position_ids — the collator's position ids on the device (bit-exact integer work).
  * Replaces src/multimeditron/model/data_loader.py:155-188:
  *   use_2d == 0:  out [batch, seq] int64 = cumsum(attention_mask) - 1, 0 where the mask is 0            (:156-157)

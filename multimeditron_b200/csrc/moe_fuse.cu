@@ -57,3 +57,106 @@ extern "C" int mm_weighted_expert_sum(const void* x, const float* w, const int32
   MM_CUDA_CHECK(cudaGetLastError());
   return MM_OK;
 }
+
+// ---- mm_cross_attention: 'cross_attn' fusion (generalist queries over the specialists' tokens) ---------------------
+// Reference: src/multimeditron/model/attention.py:48-101 (CrossAttention.forward, eval mode: both dropouts are the
+// identity; no mask on this call site: image_modality_moe.py:205, image_modality_moe_pep.py:245).
+//   out[b, i, h*hd:(h+1)*hd] = softmax_j( scale * q[b,i,h,:].k[b,j,h,:] ) @ v[b,j,h,:]
+// q [B, Nq, C] bf16, kv [B, Nkv, 2C] bf16 (columns [K | V], what ONE fused k_proj|v_proj GEMM writes), out [B, Nq, C] bf16.
+// The problem is tiny next to the experts that feed it (cfg5: 49 queries x 196 keys per image, head_dim 96 or 512 —
+// neither is a shape the tcgen05 attention kernels serve), so this is a CUDA-core kernel: one warp per query row,
+// head_dim spread over the lanes (hd/32 values per lane, hd <= 512), K/V tiles of 32 keys staged in shared memory and
+// shared by the CTA's 8 query rows, online softmax in fp32 (scores are NOT rounded to bf16 before the softmax as
+// torch.matmul does in the bf16 regime: the result is closer to the fp32 reference, inside the stated tolerance).
+namespace mm {
+constexpr int kXaWarps = 8, kXaKeys = 32, kXaMaxPerLane = 16;
+
+template <int PER_LANE>
+__global__ void __launch_bounds__(kXaWarps * 32) cross_attention_kernel(const __nv_bfloat16* __restrict__ q,
+                                                                         const __nv_bfloat16* __restrict__ kv,
+                                                                         __nv_bfloat16* __restrict__ out, int Nq, int Nkv,
+                                                                         int heads, int C, float scale_log2) {
+  constexpr int HD = PER_LANE * 32;
+  extern __shared__ __align__(16) uint8_t xa_smem[];
+  __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(xa_smem);          // [kXaKeys][HD]
+  __nv_bfloat16* sV = sK + kXaKeys * HD;                                    // [kXaKeys][HD]
+  const int b = blockIdx.x / heads, h = blockIdx.x - b * heads;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qi = blockIdx.y * kXaWarps + warp;
+  const bool live = qi < Nq;
+  float qr[PER_LANE], acc[PER_LANE];
+#pragma unroll
+  for (int t = 0; t < PER_LANE; ++t) {
+    qr[t] = live ? __bfloat162float(q[((int64_t)b * Nq + qi) * C + h * HD + t * 32 + lane]) * scale_log2 : 0.f;
+    acc[t] = 0.f;
+  }
+  float m = -INFINITY, l = 0.f;
+  for (int j0 = 0; j0 < Nkv; j0 += kXaKeys) {
+    const int nk = min(kXaKeys, Nkv - j0);
+    __syncthreads();
+    // stage K and V rows j0..j0+nk of head h: 16-byte vectors
+    for (int v = threadIdx.x; v < nk * (HD / 8) * 2; v += blockDim.x) {
+      const int which = v / (nk * (HD / 8));
+      const int r = (v - which * nk * (HD / 8)) / (HD / 8), c8 = v % (HD / 8);
+      const int4 val = __ldg(reinterpret_cast<const int4*>(kv + ((int64_t)b * Nkv + j0 + r) * (2 * C) + which * C + h * HD) + c8);
+      reinterpret_cast<int4*>((which ? sV : sK) + r * HD)[c8] = val;
+    }
+    __syncthreads();
+    if (live) {
+      for (int j = 0; j < nk; ++j) {
+        float s = 0.f;
+#pragma unroll
+        for (int t = 0; t < PER_LANE; ++t) s = fmaf(qr[t], __bfloat162float(sK[j * HD + t * 32 + lane]), s);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        const float m_new = fmaxf(m, s);
+        const float alpha = exp2f(m - m_new), p = exp2f(s - m_new);
+        l = l * alpha + p;
+#pragma unroll
+        for (int t = 0; t < PER_LANE; ++t)
+          acc[t] = fmaf(p, __bfloat162float(sV[j * HD + t * 32 + lane]), acc[t] * alpha);
+        m = m_new;
+      }
+    }
+  }
+  if (live) {
+    const float inv = 1.0f / l;
+#pragma unroll
+    for (int t = 0; t < PER_LANE; ++t)
+      out[((int64_t)b * Nq + qi) * C + h * HD + t * 32 + lane] = __float2bfloat16_rn(acc[t] * inv);
+  }
+}
+
+template <int PER_LANE>
+static int launch_cross_attention(const void* q, const void* kv, void* out, int64_t B, int64_t Nq, int64_t Nkv,
+                                  int64_t heads, int64_t C, float scale, cudaStream_t st) {
+  constexpr int HD = PER_LANE * 32;
+  const size_t smem = 2 * (size_t)kXaKeys * HD * sizeof(__nv_bfloat16);
+  dim3 grid((unsigned)(B * heads), (unsigned)((Nq + kXaWarps - 1) / kXaWarps));
+  cross_attention_kernel<PER_LANE><<<grid, kXaWarps * 32, smem, st>>>(
+      reinterpret_cast<const __nv_bfloat16*>(q), reinterpret_cast<const __nv_bfloat16*>(kv),
+      reinterpret_cast<__nv_bfloat16*>(out), (int)Nq, (int)Nkv, (int)heads, (int)C, scale * 1.4426950408889634f);
+  MM_CUDA_CHECK(cudaGetLastError());
+  return MM_OK;
+}
+}  // namespace mm
+
+extern "C" int mm_cross_attention(const void* q, const void* kv, void* out, int64_t B, int64_t Nq, int64_t Nkv,
+                                  int64_t heads, int64_t C, float scale, void* stream) {
+  using namespace mm;
+  if (B < 0 || Nq <= 0 || Nkv <= 0 || heads <= 0 || C <= 0 || C % heads) return MM_ERR_BAD_ARG;
+  const int64_t hd = C / heads;
+  if (hd % 32 || hd > 32 * kXaMaxPerLane || hd % 8) return MM_ERR_BAD_ARG;
+  if (B == 0) return MM_OK;
+  if (!q || !kv || !out || (reinterpret_cast<uintptr_t>(kv) & 15)) return MM_ERR_BAD_ARG;
+  if (B * heads > 2147483647LL || (Nq + kXaWarps - 1) / kXaWarps > 65535) return MM_ERR_BAD_ARG;
+  if (!(scale > 0.f)) return MM_ERR_BAD_ARG;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  switch (hd / 32) {
+#define MM_XA_CASE(n) case n: return launch_cross_attention<n>(q, kv, out, B, Nq, Nkv, heads, C, scale, st);
+    MM_XA_CASE(1) MM_XA_CASE(2) MM_XA_CASE(3) MM_XA_CASE(4) MM_XA_CASE(5) MM_XA_CASE(6) MM_XA_CASE(7) MM_XA_CASE(8)
+    MM_XA_CASE(9) MM_XA_CASE(10) MM_XA_CASE(11) MM_XA_CASE(12) MM_XA_CASE(13) MM_XA_CASE(14) MM_XA_CASE(15) MM_XA_CASE(16)
+#undef MM_XA_CASE
+  }
+  return MM_ERR_BAD_ARG;
+}

@@ -119,9 +119,9 @@ class _B200MOEBase(BaseModality):
         self._native_embed_dim = t0.hidden_size
         self.generalist_idx = config.generalist_idx
         self.fusion_method = config.fusion_method
-        if self.fusion_method.replace("-", "_") == "cross_attn":
-            raise NotImplementedError("cross_attn fusion (model/attention.py:48-101) is SURVEY.md §8(f)#3 (next)")
-        if self.fusion_method not in ("weighted_average", "sequence_append"):
+        if self.fusion_method.replace("-", "_") == "cross_attn":     # image_modality_moe.py:141 accepts both spellings
+            self.fusion_method = "cross_attn"
+        if self.fusion_method not in ("weighted_average", "sequence_append", "cross_attn"):
             raise ValueError(f"Unsupported fusion_method: {self.fusion_method}")
         # perm[class_idx] = expert_idx (image_modality_moe.py:125-138)
         names = getattr(config, "gating_class_names", None) or []
@@ -166,6 +166,13 @@ class _B200MOEBase(BaseModality):
             self._projs = [ProjectorWeights(sd, dev, "projector.")]
         self._device = dev
         self._perm = torch.tensor(self._perm_list, dtype=torch.int32, device=dev)
+        self._xattn = None
+        if self.fusion_method == "cross_attn":    # CrossAttention parameters (attention.py:36-42), k|v fused into one GEMM
+            g = lambda n: sd["cross_attn." + n].detach().to(device=dev, dtype=torch.bfloat16).contiguous()  # noqa: E731
+            self._xattn = dict(wq=g("q_proj.weight"), bq=g("q_proj.bias"),
+                               wkv=torch.cat([g("k_proj.weight"), g("v_proj.weight")], 0).contiguous(),
+                               bkv=torch.cat([g("k_proj.bias"), g("v_proj.bias")], 0).contiguous(),
+                               wo=g("proj.weight"), bo=g("proj.bias"))
         if gating is not None:
             self._gating = gating
         return self
@@ -211,14 +218,15 @@ class _B200MOEBase(BaseModality):
             raise RuntimeError(f"gating returned weights of shape {tuple(w.shape)}, expected {(px.shape[0], E)}")
         return w.to(device=self._device, dtype=torch.float32).contiguous()
 
-    def _append_map(self, B: int, e: int) -> torch.Tensor:
+    def _append_map(self, B: int, e: int, E: Optional[int] = None) -> torch.Tensor:
         """compact row (b*P+p) of expert e -> row ((b*E+e)*P+p) of the [B,E,P,*] stack."""
-        key = (B, e)
+        E = len(self.towers) if E is None else E
+        key = (B, e, E)
         m = self._maps.get(key)
         if m is None:
             if len(self._maps) > 64:
                 self._maps.clear()
-            E, P = len(self.towers), self._num_patches_per_entry
+            P = self._num_patches_per_entry
             r = torch.arange(B * P, device=self._device, dtype=torch.int64)
             m = (((r // P) * E + e) * P + r % P).to(torch.int32)
             self._maps[key] = m
@@ -247,6 +255,29 @@ class _B200MOEBase(BaseModality):
     def _release(self):
         if self._pre is not None and self._pre.uploader is not None:
             self._pre.uploader.release()
+
+    def _cross_attn_fuse(self, stack: torch.Tensor, w: torch.Tensor, B: int, P: int) -> torch.Tensor:
+        """image_modality_moe.py:178-205 / image_modality_moe_pep.py:218-245 on `stack` [E, B*P, C]:
+        generalist tokens (python index `generalist_idx`, -1 = last expert) query the gate-weighted tokens of every
+        expert i with `i != generalist_idx` — the reference compares the RAW index, so with the default -1 the generalist
+        is also one of the "specialists"; reproduced as is.  Gate weights: permuted to expert order (both variants do it
+        here, :190 / :230), re-softmaxed over the specialists in the tensor dtype, multiplied into the tokens (bf16
+        products), k|v projected by ONE GEMM straight into the [B, S*P, 2C] layout, attention (mm_cross_attention),
+        output projection."""
+        E, _, C = stack.shape
+        gi = self.generalist_idx
+        spec = [i for i in range(E) if i != gi]
+        xa = self._xattn
+        w_all = w.to(torch.bfloat16).index_select(-1, self._perm.long())               # [B, E] in expert order
+        w_spec = torch.softmax(w_all[:, spec], dim=-1).float().contiguous()               # bf16 values, held as fp32
+        S = len(spec)
+        kv = torch.empty(B, S * P, 2 * C, dtype=torch.bfloat16, device=self._device)
+        for j, e in enumerate(spec):
+            ctx = ops.weighted_expert_sum(stack[e:e + 1], w_spec[:, j:j + 1].contiguous(), None, B, P)   # ctx * wj
+            ops.gemm_bias_act(ctx, xa["wkv"], xa["bkv"], out=kv.view(-1, 2 * C), out_row_map=self._append_map(B, j, S))
+        q = ops.gemm_bias_act(stack[gi], xa["wq"], xa["bq"])                              # [B*P, C]
+        a = ops.cross_attention(q.view(B, P, C), kv, self.config.cross_attn_heads)
+        return ops.gemm_bias_act(a.view(B * P, C), xa["wo"], xa["bo"])
 
     def _each_expert(self, fn):
         """Run fn(e, runner) for every expert, expert e on its own CUDA stream (fork from / join into the current
@@ -311,6 +342,12 @@ class B200MOEImageModality(_B200MOEBase):
             w = self._weights(px)                                                  # :156 (overlaps the experts)
             self._join_experts()
             fused = ops.weighted_expert_sum(stack, w, self._perm, B, P)            # :171-177 (permuted weights)
+        elif self.fusion_method == "cross_attn":                                   # :178-205
+            stack = torch.empty(E, B * P, D, dtype=torch.bfloat16, device=self._device)
+            self._each_expert(lambda e, r: r.features(px, out=stack[e]))
+            w = self._weights(px)
+            self._join_experts()
+            fused = self._cross_attn_fuse(stack, w, B, P)
         else:                                                                      # sequence_append :167-169
             fused = torch.empty(B * E * P, D, dtype=torch.bfloat16, device=self._device)
             maps = [self._append_map(B, e) for e in range(E)]
@@ -334,6 +371,16 @@ class B200MOEImageModalityPEP(_B200MOEBase):
             w = self._weights(px)                                                  # :194 (overlaps the experts)
             self._join_experts()
             fused = ops.weighted_expert_sum(stack, w, None, B, P)                  # :212-216 (NO permutation)
+            if dest_rows is None:
+                out2d.copy_(fused)
+            else:
+                ops.splice_scatter(out2d, fused, dest_rows)
+        elif self.fusion_method == "cross_attn":                                   # :218-245 (in the projected space)
+            stack = torch.empty(E, B * P, H, dtype=torch.bfloat16, device=self._device)
+            self._each_expert(lambda e, r: r.project(r.features(px), self._projs[e], out=stack[e]))
+            w = self._weights(px)
+            self._join_experts()
+            fused = self._cross_attn_fuse(stack, w, B, P)
             if dest_rows is None:
                 out2d.copy_(fused)
             else:

@@ -396,6 +396,22 @@ def weighted_expert_sum(x: torch.Tensor, w: torch.Tensor, perm: torch.Tensor | N
     return out
 
 
+def cross_attention(q: torch.Tensor, kv: torch.Tensor, heads: int, scale: float | None = None) -> torch.Tensor:
+    """q [B,Nq,C] bf16, kv [B,Nkv,2C] bf16 ([K | V] columns) -> [B,Nq,C] bf16 (attention.py:48-101, eval, no mask)."""
+    _cuda(q, kv)
+    lib = _lib.load()
+    B, Nq, Cc = q.shape
+    assert kv.shape[0] == B and kv.shape[2] == 2 * Cc and q.is_contiguous() and kv.is_contiguous()
+    assert q.dtype == torch.bfloat16 and kv.dtype == torch.bfloat16
+    Nkv = kv.shape[1]
+    out = torch.empty_like(q)
+    sc = float(scale) if scale is not None else (Cc // heads) ** -0.5
+    with _timed("mm_cross_attention", 4.0 * B * Nq * Nkv * Cc):
+        rc = lib.mm_cross_attention(_ptr(q), _ptr(kv), _ptr(out), B, Nq, Nkv, int(heads), Cc, sc, _stream())
+    _check(rc, "mm_cross_attention")
+    return out
+
+
 def position_ids(attention_mask: torch.Tensor, input_ids: torch.Tensor | None = None, attachment_id: int = -1,
                  tokens_per_image: int = 0, grid: int = 0, use_2d: bool = False,
                  status: torch.Tensor | None = None) -> torch.Tensor:

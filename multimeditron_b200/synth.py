@@ -93,7 +93,7 @@ def add_massive_activations(sd: dict, cfg: TowerConfig, seed: int = 0, frac: flo
 
 
 def make_moe_state_dict(towers, llm_hidden: int, per_expert_projector: bool, seed: int = 0, dtype=torch.float32,
-                        device="cpu"):
+                        device="cpu", cross_attn: bool = False):
     """State dict of a MoE modality (image_modality_moe.py / image_modality_moe_pep.py): `experts.<i>.*` holds the HF
     CLIPVisionTransformer of expert i, `projector.*` (shared) or `projectors.<i>.*` (PEP) the MLP projectors."""
     gen = torch.Generator().manual_seed(seed)
@@ -104,7 +104,17 @@ def make_moe_state_dict(towers, llm_hidden: int, per_expert_projector: bool, see
             keys += projector_keys(cfg.hidden_size, llm_hidden, prefix=f"projectors.{i}.")
     if not per_expert_projector:
         keys += projector_keys(towers[0].hidden_size, llm_hidden, prefix="projector.")
-    return _draw(keys, gen, dtype, device)
+    sd = _draw(keys, gen, dtype, device)
+    if cross_attn:   # CrossAttention (attention.py:36-42): dim = experts' width (shared) or the LLM hidden size (PEP)
+        C = llm_hidden if per_expert_projector else towers[0].hidden_size
+        xk = []
+        for n in ("q_proj", "k_proj", "v_proj", "proj"):
+            xk += [(f"cross_attn.{n}.weight", (C, C), "w"), (f"cross_attn.{n}.bias", (C,), "x")]
+        xs = _draw(xk, gen, torch.float32, "cpu")  # drawn AFTER the rest: the other tensors do not depend on the flag
+        for n in ("q_proj", "k_proj"):             # N(0, 0.06): scores spread enough for a non-uniform softmax
+            xs[f"cross_attn.{n}.weight"] *= 3.0
+        sd.update({k: v.to(dtype).to(device) for k, v in xs.items()})
+    return sd
 
 
 def make_pixels(cfg: TowerConfig, batch: int, seed: int = 0, device="cpu"):

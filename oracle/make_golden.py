@@ -327,6 +327,11 @@ MOE_CASES = [  # name, per-expert projector, fusion, experts, hidden, batch, wei
     # CLIP ViT-B/32-sized experts (the cfg5 expert shape: D 768, 12 layers, 12 heads, T = 50) -> hidden 512
     ("moe_shared_avg_b32", False, "weighted_average", 3, 512, 2, 31, 9, "clip_b32"),
     ("moe_pep_avg_b32", True, "weighted_average", 3, 512, 2, 33, 10, "clip_b32"),
+    # cross_attn fusion (attention.py:48-101): tiny (dim 128 / 64, 2 heads -> head_dim 64 / 32), generalist_idx 1 and the
+    # default -1 (where the raw-index comparison makes every expert a "specialist"); ViT-B/32 experts: 8 heads x 96
+    ("moe_shared_xattn", False, "cross_attn", 3, 64, 3, 41, 11, "tiny", 1, 2),
+    ("moe_pep_xattn", True, "cross_attn", 3, 64, 2, 42, 12, "tiny", -1, 2),
+    ("moe_shared_xattn_b32", False, "cross_attn", 3, 512, 2, 43, 13, "clip_b32", -1, 8),
 ]
 MOE_CLASS_ORDER = [2, 0, 1]   # gating class c is expert MOE_CLASS_ORDER[c]  (non-identity on purpose)
 
@@ -356,6 +361,8 @@ def gen_moe(ref):
     for case in MOE_CASES:
         name, pep, fusion, E, hidden, batch, wseed, pseed = case[:8]
         tower = case[8] if len(case) > 8 else "tiny"
+        gen_idx, xheads = (case[9], case[10]) if len(case) > 10 else (-1, 8)
+        xattn = fusion == "cross_attn"
         if only and only not in name:
             continue
         cfg = TOWERS[tower]
@@ -366,9 +373,10 @@ def gen_moe(ref):
                                           class_names=[dirs[i] for i in MOE_CLASS_ORDER])).save_pretrained(gdir)
         Cfg, Mod = (MOEImageConfigPEP, MOEImageModalityPEP) if pep else (MOEImageConfig, MOEImageModality)
         m = Mod(Cfg(hidden_size=hidden, expert_clip_names=dirs, image_processor=dirs[0], gating_path=gdir,
-                    top_k_experts=E if fusion == "sequence_append" else 1, fusion_method=fusion)).eval()
+                    top_k_experts=E if fusion == "sequence_append" else 1, fusion_method=fusion,
+                    generalist_idx=gen_idx, cross_attn_heads=xheads)).eval()
         m = m.float()   # the MoE projectors are hard-defaulted to bf16 (projectors/mlp.py:16): cast BEFORE loading
-        sd32 = synth.make_moe_state_dict([cfg] * E, hidden, pep, seed=wseed)
+        sd32 = synth.make_moe_state_dict([cfg] * E, hidden, pep, seed=wseed, cross_attn=xattn)
         missing, unexpected = m.load_state_dict(sd32, strict=False)
         assert not unexpected, unexpected
         assert all(k.startswith("gating_network.") for k in missing), missing
@@ -380,22 +388,24 @@ def gen_moe(ref):
         y32 = m(inputs)
         perm = m._gating_to_expert_perm.tolist()
         assert perm == MOE_CLASS_ORDER
-        o32 = vit_oracle.moe_modality_forward(sd32, [cfg] * E, inputs, w32, perm, fusion, pep)
+        o32 = vit_oracle.moe_modality_forward(sd32, [cfg] * E, inputs, w32, perm, fusion, pep, gen_idx, xheads)
         assert torch.equal(y32, o32), f"{name}: oracle != reference (fp32)"
         mb = m.to(torch.bfloat16)
         _, _, wb = mb.gating_network(pixels.to(torch.bfloat16))
         yb = mb([p.to(torch.bfloat16) for p in inputs])
         sdb = {k: v.to(torch.bfloat16) for k, v in sd32.items()}
-        ob = vit_oracle.moe_modality_forward(sdb, [cfg] * E, [p.to(torch.bfloat16) for p in inputs], wb, perm, fusion, pep)
+        ob = vit_oracle.moe_modality_forward(sdb, [cfg] * E, [p.to(torch.bfloat16) for p in inputs], wb, perm, fusion, pep,
+                                             gen_idx, xheads)
         assert torch.equal(yb, ob), f"{name}: oracle != reference (bf16)"
         # the reference's own bf16 error with the SAME gating weights as the fp32 run (isolates tower/projector rounding)
         ob_w32 = vit_oracle.moe_modality_forward(sdb, [cfg] * E, [p.to(torch.bfloat16) for p in inputs],
-                                                 w32.to(torch.bfloat16), perm, fusion, pep)
+                                                 w32.to(torch.bfloat16), perm, fusion, pep, gen_idx, xheads)
         err = (ob_w32.float() - y32).abs().max().item()
         print(f"[{name}] out {tuple(y32.shape)} absmax {y32.abs().max():.4f} bf16-vs-fp32 maxabs {err:.3e} "
               f"weights {w32[0].tolist()}")
         np.savez_compressed(os.path.join(GOLD, f"{name}.npz"), pep=pep, fusion=fusion, experts=E, hidden=hidden,
                             batch=batch, wseed=wseed, pseed=pseed, perm=np.array(perm), weights32=w32.numpy(), tower=tower,
+                            generalist_idx=gen_idx, cross_attn_heads=xheads,
                             out_fp32=y32.numpy(), out_bf16_w32_bits=bf16_bits(ob_w32))
 
 

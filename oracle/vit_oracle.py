@@ -117,7 +117,7 @@ def moe_weighted_average(expert_feats: torch.Tensor, weights: torch.Tensor, perm
 
 
 def moe_modality_forward(sd, towers, inputs, weights: torch.Tensor, perm, fusion_method: str,
-                         per_expert_projector: bool) -> torch.Tensor:
+                         per_expert_projector: bool, generalist_idx: int = -1, cross_attn_heads: int = 8) -> torch.Tensor:
     """image_modality_moe.py:152-210 (shared projector: weights permuted :171-175, projector after fusion :207) and
     image_modality_moe_pep.py:191-249 (projector per expert :198-203, NO permutation :212-216).
     `weights` [B,E] = the gating network's softmax output (moe/gating.py:85-87) — an input here."""
@@ -136,6 +136,38 @@ def moe_modality_forward(sd, towers, inputs, weights: torch.Tensor, perm, fusion
         if not per_expert_projector:
             w = w.index_select(dim=-1, index=torch.as_tensor(perm, dtype=torch.long))
         fused = (stacked * w.unsqueeze(-1).unsqueeze(-1)).sum(dim=1)
+    elif fusion_method == "cross_attn":
+        fused = cross_attn_fusion(sd, stacked, weights, perm, generalist_idx, cross_attn_heads)
     else:
         raise ValueError(f"Unsupported fusion_method: {fusion_method}")
     return fused if per_expert_projector else mlp_projector(sd, fused, prefix="projector.")
+
+
+def cross_attention(sd, x: torch.Tensor, experts, num_heads: int, prefix: str = "cross_attn.") -> torch.Tensor:
+    """src/multimeditron/model/attention.py:48-101 in eval mode (both dropouts are the identity), no mask."""
+    B, N_q, C = x.shape
+    hd = C // num_heads
+    context = torch.cat(experts, dim=1)                                               # :67
+    N_kv = context.shape[1]
+    q = F.linear(x, sd[prefix + "q_proj.weight"], sd[prefix + "q_proj.bias"])          # :71-73
+    k = F.linear(context, sd[prefix + "k_proj.weight"], sd[prefix + "k_proj.bias"])
+    v = F.linear(context, sd[prefix + "v_proj.weight"], sd[prefix + "v_proj.bias"])
+    q = q.view(B, N_q, num_heads, hd).transpose(1, 2)                                  # :76-78
+    k = k.view(B, N_kv, num_heads, hd).transpose(1, 2)
+    v = v.view(B, N_kv, num_heads, hd).transpose(1, 2)
+    attn = torch.matmul(q, k.transpose(-2, -1)) * (hd ** -0.5)                         # :81
+    attn = torch.softmax(attn, dim=-1)                                                 # :91
+    out = torch.matmul(attn, v).transpose(1, 2).reshape(B, N_q, C)                     # :95-98
+    return F.linear(out, sd[prefix + "proj.weight"], sd[prefix + "proj.bias"])         # :99
+
+
+def cross_attn_fusion(sd, stacked: torch.Tensor, weights: torch.Tensor, perm, generalist_idx: int, num_heads: int):
+    """image_modality_moe.py:178-205 == image_modality_moe_pep.py:218-245: generalist queries over gate-weighted
+    specialists.  `i != generalist_idx` compares the RAW index (with the default -1 every expert is a specialist)."""
+    B, E, P, C = stacked.shape
+    q = stacked[:, generalist_idx, :, :]
+    spec = [i for i in range(E) if i != generalist_idx]
+    w_all = weights.index_select(dim=-1, index=torch.as_tensor(perm, dtype=torch.long, device=weights.device))
+    w_spec = torch.softmax(w_all[:, spec], dim=-1)
+    ctx = [stacked[:, e, :, :] * w_spec[:, j].view(B, 1, 1) for j, e in enumerate(spec)]
+    return cross_attention(sd, q, ctx, num_heads)

@@ -16,7 +16,8 @@ from oracle import splice_oracle
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
 MOE_NAMES = ["moe_shared_avg", "moe_shared_append", "moe_pep_avg", "moe_pep_append",
-             "moe_shared_avg_b32", "moe_pep_avg_b32"]       # *_b32: CLIP ViT-B/32-sized experts (the cfg5 expert shape)
+             "moe_shared_avg_b32", "moe_pep_avg_b32",       # *_b32: CLIP ViT-B/32-sized experts (the cfg5 expert shape)
+             "moe_shared_xattn", "moe_pep_xattn", "moe_shared_xattn_b32"]   # cross_attn fusion (attention.py:48-101)
 
 
 def _build(g):
@@ -29,8 +30,11 @@ def _build(g):
         "model_type": "moe_meditron_clip_pep_b200" if pep else "moe_meditron_clip_b200", "hidden_size": hidden,
         "expert_clip_names": names, "expert_towers": {n: tower for n in names}, "image_processor": tower,
         "fusion_method": str(g["fusion"]), "top_k_experts": E if str(g["fusion"]) == "sequence_append" else 1,
-        "gating_class_names": [names[i] for i in perm]})
-    sd = synth.make_moe_state_dict([cfg] * E, hidden, pep, seed=int(g["wseed"]))
+        "gating_class_names": [names[i] for i in perm],
+        "generalist_idx": int(g["generalist_idx"]) if "generalist_idx" in g.files else -1,
+        "cross_attn_heads": int(g["cross_attn_heads"]) if "cross_attn_heads" in g.files else 8})
+    sd = synth.make_moe_state_dict([cfg] * E, hidden, pep, seed=int(g["wseed"]),
+                                   cross_attn=str(g["fusion"]) == "cross_attn")
     w = torch.from_numpy(g["weights32"])
     m = AutoModality.from_config(mcfg).load_reference_state_dict(sd, DEV, gating=lambda px: w.to(px.device))
     return m, cfg

@@ -110,7 +110,8 @@ def test_c_oracle_agrees_with_numpy_oracle():
     assert np.array_equal(out, want)
 
 
-MOE_NAMES = ["moe_shared_avg", "moe_shared_append", "moe_pep_avg", "moe_pep_append", "moe_shared_avg_b32", "moe_pep_avg_b32"]
+MOE_NAMES = ["moe_shared_avg", "moe_shared_append", "moe_pep_avg", "moe_pep_append", "moe_shared_avg_b32", "moe_pep_avg_b32",
+             "moe_shared_xattn", "moe_pep_xattn", "moe_shared_xattn_b32"]
 
 
 @pytest.mark.parametrize("name", MOE_NAMES)
@@ -120,12 +121,15 @@ def test_moe_oracle_matches_reference_golden(golden_dir, name):
     g = np.load(os.path.join(golden_dir, f"{name}.npz"))
     cfg = TOWERS[str(g["tower"]) if "tower" in g.files else "tiny"]
     E, hidden, batch, pep = int(g["experts"]), int(g["hidden"]), int(g["batch"]), bool(g["pep"])
-    sd = synth.make_moe_state_dict([cfg] * E, hidden, pep, seed=int(g["wseed"]))
+    xattn = str(g["fusion"]) == "cross_attn"
+    gi, xh = (int(g["generalist_idx"]), int(g["cross_attn_heads"])) if "generalist_idx" in g.files else (-1, 8)
+    sd = synth.make_moe_state_dict([cfg] * E, hidden, pep, seed=int(g["wseed"]), cross_attn=xattn)
     px = synth.make_pixels(cfg, batch, seed=int(g["pseed"]))
     perm = g["perm"].tolist()
     assert perm != sorted(perm)
     with torch.no_grad():
-        y = vit_oracle.moe_modality_forward(sd, [cfg] * E, px, torch.from_numpy(g["weights32"]), perm, str(g["fusion"]), pep)
+        y = vit_oracle.moe_modality_forward(sd, [cfg] * E, px, torch.from_numpy(g["weights32"]), perm, str(g["fusion"]), pep,
+                                            gi, xh)
         ref = torch.from_numpy(g["out_fp32"])
         assert y.shape == ref.shape
         assert torch.allclose(y, ref, rtol=0, atol=2e-5 * ref.abs().max().item())
