@@ -238,7 +238,7 @@ class _B200MOEBase(BaseModality):
         """-> [B, P, H] (weighted_average) or [B, E*P, H] (sequence_append), bf16."""
         px = self._stack(inputs)
         B, E, P, H = px.shape[0], len(self.towers), self._num_patches_per_entry, self.config.hidden_size
-        n_out = P if self.fusion_method == "weighted_average" else E * P
+        n_out = E * P if self.fusion_method == "sequence_append" else P
         out = torch.empty(B, n_out, H, dtype=torch.bfloat16, device=self._device)
         self._run(px, out.view(-1, H), None)
         self._release()
