@@ -16,7 +16,7 @@ import torch
 
 class ResNet50Gate(torch.nn.Module):
     def __init__(self, num_classes: int, top_k: int = 1, device=None, dtype=torch.bfloat16,
-                 state_dict: Optional[dict] = None, prefix: str = "resnet."):
+                 state_dict: Optional[dict] = None, prefix: str = "resnet.", fold_bn: bool = True):
         super().__init__()
         from torchvision import models                      # gating.py:60-65
         self.resnet = models.resnet50(weights=None)
@@ -26,6 +26,10 @@ class ResNet50Gate(torch.nn.Module):
             own = {k[len(prefix):]: v for k, v in state_dict.items() if k.startswith(prefix)}
             self.resnet.load_state_dict(own)
         self.resnet.eval()
+        if fold_bn:
+            # eval-mode BatchNorm is an affine map per channel: fold it into the preceding convolution's weight and bias
+            # (in fp32, before the bf16 cast) — one cuDNN conv per layer instead of conv + a memory-bound BN pass
+            self.resnet = _fold_batchnorm(self.resnet)
         self.to(device=device, dtype=dtype, memory_format=torch.channels_last)
         self._dtype = dtype
 
@@ -37,3 +41,22 @@ class ResNet50Gate(torch.nn.Module):
         _, topk_indices = torch.topk(logits, self.top_k, dim=-1)
         weights = torch.nn.functional.softmax(logits, dim=-1)
         return logits, topk_indices, weights
+
+
+def _fold_batchnorm(net: torch.nn.Module) -> torch.nn.Module:
+    """conv -> bn pairs of a torchvision ResNet (conv1/bn1, every Bottleneck's conv{1,2,3}/bn{1,2,3}, downsample[0]/[1])."""
+    from torch.nn.utils.fusion import fuse_conv_bn_eval
+
+    def fold(parent, conv_name, bn_name):
+        conv, bn = getattr(parent, conv_name), getattr(parent, bn_name)
+        setattr(parent, conv_name, fuse_conv_bn_eval(conv, bn))
+        setattr(parent, bn_name, torch.nn.Identity())
+
+    fold(net, "conv1", "bn1")
+    for layer in (net.layer1, net.layer2, net.layer3, net.layer4):
+        for blk in layer:
+            for i in (1, 2, 3):
+                fold(blk, f"conv{i}", f"bn{i}")
+            if blk.downsample is not None:
+                blk.downsample = torch.nn.Sequential(fuse_conv_bn_eval(blk.downsample[0], blk.downsample[1]))
+    return net

@@ -148,3 +148,21 @@ def test_moe_plugin_contract_on_cpu():
             {"model_type": "moe_meditron_clip_b200", "hidden_size": 64, "expert_clip_names": []}))
     with pytest.raises(RuntimeError):    # no weights loaded -> loud failure, no fallback
         m([torch.zeros(3, 32, 32)])
+
+
+def test_gate_batchnorm_fold_is_exact_in_fp32():
+    """gating.ResNet50Gate folds eval-mode BatchNorm into the convolutions: same logits as the unfused torchvision net."""
+    pytest.importorskip("torchvision")
+    from multimeditron_b200.gating import ResNet50Gate
+    torch.manual_seed(0)
+    a = ResNet50Gate(3, device="cpu", dtype=torch.float32, fold_bn=False)
+    for m in a.resnet.modules():
+        if isinstance(m, torch.nn.BatchNorm2d):
+            m.running_mean.normal_(0, 0.1); m.running_var.uniform_(0.5, 1.5)
+            m.weight.data.uniform_(0.5, 1.5); m.bias.data.normal_(0, 0.1)
+    sd = {"resnet." + k: v for k, v in a.resnet.state_dict().items()}
+    b = ResNet50Gate(3, device="cpu", dtype=torch.float32, state_dict=sd, fold_bn=True)
+    x = torch.randn(1, 3, 224, 224)
+    la, ta, wa = a(x)
+    lb, tb, wb = b(x)
+    assert (la - lb).abs().max().item() <= 1e-5 * la.abs().max().item() and torch.equal(ta, tb)

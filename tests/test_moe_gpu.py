@@ -85,3 +85,25 @@ def test_moe_splice_fused_equals_unfused(golden_dir, name):
     want = splice_oracle.embed_modalities_with_text(table.cpu(), ids, pmi["batch_idx"]["image"],
                                                     pmi["token_range"]["image"], proj)
     assert torch.equal(outs[0].cpu(), want)
+
+
+def test_resnet50_gate_matches_the_reference_gating_network():
+    """moe/gating.py:73-89: ResNet-50 logits -> top-k -> softmax.  The device gate (bf16, channels-last, BatchNorm folded
+    into the convolutions) against the same torchvision network run unfused in fp32 (what GatingNetwork executes)."""
+    pytest.importorskip("torchvision")
+    from multimeditron_b200.gating import ResNet50Gate
+    torch.manual_seed(3)
+    ref = ResNet50Gate(5, top_k=2, device=DEV, dtype=torch.float32, fold_bn=False)
+    for m in ref.resnet.modules():          # non-trivial running statistics / affine parameters
+        if isinstance(m, torch.nn.BatchNorm2d):
+            m.running_mean.normal_(0, 0.1); m.running_var.uniform_(0.5, 1.5)
+            m.weight.data.uniform_(0.5, 1.5); m.bias.data.normal_(0, 0.1)
+    sd = {"gating_network.resnet." + k: v for k, v in ref.resnet.state_dict().items()}
+    gate = ResNet50Gate(5, top_k=2, device=DEV, state_dict=sd, prefix="gating_network.resnet.")
+    px = torch.randn(6, 3, 224, 224, device=DEV)
+    l32, t32, w32 = ref(px)
+    l, t, w = gate(px.bfloat16())
+    assert w.shape == (6, 5) and t.shape == (6, 2)
+    assert torch.allclose(w.float().sum(-1), torch.ones(6, device=DEV), atol=2e-2)
+    scale = l32.abs().max().item()
+    assert (l.float() - l32).abs().max().item() <= 5e-2 * scale
