@@ -134,7 +134,7 @@ def moe_modality_forward(sd, towers, inputs, weights: torch.Tensor, perm, fusion
     elif fusion_method == "weighted_average":
         w = weights
         if not per_expert_projector:
-            w = w.index_select(dim=-1, index=torch.as_tensor(perm, dtype=torch.long))
+            w = w.index_select(dim=-1, index=torch.as_tensor(perm, dtype=torch.long, device=w.device))
         fused = (stacked * w.unsqueeze(-1).unsqueeze(-1)).sum(dim=1)
     elif fusion_method == "cross_attn":
         fused = cross_attn_fusion(sd, stacked, weights, perm, generalist_idx, cross_attn_heads)
