@@ -139,6 +139,60 @@ def register_with_reference():
     return cls
 
 
+@torch.no_grad()
+def b200_generate(model, batch: Dict[str, Any], max_new_tokens: int = 512, temperature: float = 0.1,
+                  do_sample: bool = True, sync_every: int = 16, output_attentions: bool = True, **kwargs) -> torch.Tensor:
+    """`MultiModalModelForCausalLM.generate` (model.py:528-640) without its per-token host round trips (SURVEY §8(f)
+    rank 4).  Same arguments, same return value (`[batch, n_generated]` int64 on the host), same stopping rule; the LLM
+    call itself is the reference's (`self.model(inputs_embeds=..., past_key_values=..., use_cache=True)`).  Differences,
+    all outside the arithmetic:
+      * the sampled / arg-max token, the finished mask and the generated ids stay ON THE DEVICE (the reference calls
+        `.cpu()` on every token, samples row by row in a Python loop, and patches finished rows on the host, :611-628);
+      * "all rows finished" is tested on the host only every `sync_every` steps; the tokens generated past the step
+        where the reference would have stopped are cut off afterwards, so the result is the same;
+      * the next token's embedding row comes from `mm_embed_gather`, the attention mask is one preallocated buffer.
+    Greedy decoding is token-for-token identical to the reference; with `do_sample` one batched `torch.multinomial`
+    replaces the per-row calls (same distribution, different draw order from the generator).
+    `output_attentions=True` is what the reference passes to the LLM (:598; it makes HF use its eager attention); keep
+    it for bit-identical logits, pass False to let the LLM use SDPA."""
+    input_ids = batch["input_ids"]
+    pmi = batch["processed_multimodal_inputs"]
+    temperature = max(temperature, 1e-6)
+    device = model.model.device
+    B = input_ids.shape[0]
+    eos = int(model.config.eos_token_idx)
+    emb = model.embed_modalities_with_text(input_ids if hasattr(model, "b200_state") else input_ids.to(device), pmi)
+    table = model.model.get_input_embeddings().weight
+    attn0 = batch["attention_mask"].to(device)
+    position_ids = batch["position_ids"].to(device)
+    S = attn0.shape[1]
+    mask = torch.ones(B, S + max_new_tokens, dtype=attn0.dtype, device=device)
+    mask[:, :S] = attn0
+    tokens = torch.full((max_new_tokens, B), eos, dtype=torch.long, device=device)
+    finished = torch.zeros(B, dtype=torch.bool, device=device)
+    all_done_at = torch.full((1,), max_new_tokens, dtype=torch.long, device=device)   # first step after which all rows are done
+    past = None
+    n = 0
+    for i in range(max_new_tokens):
+        if i > 0:
+            position_ids = torch.full((B, 1), S + i - 1, dtype=torch.long, device=device)          # :585-588
+        out = model.model(inputs_embeds=emb, attention_mask=mask[:, :S + i], position_ids=position_ids,
+                          past_key_values=past, use_cache=True, output_attentions=output_attentions)
+        past = out.past_key_values
+        probs = torch.softmax(out.logits[:, -1, :] / temperature, dim=-1)                           # :605-607
+        nxt = torch.multinomial(probs, 1).view(B) if do_sample else torch.argmax(probs, dim=-1)
+        nxt = torch.where(finished, torch.full_like(nxt, eos), nxt)                                 # :620-622
+        tokens[i] = nxt
+        finished = finished | (nxt == eos)                                                          # :627-628
+        all_done_at = torch.minimum(all_done_at, torch.where(finished.all(), i, max_new_tokens).view(1))
+        n = i + 1
+        if (i + 1) % sync_every == 0 and bool(finished.all()):                                      # :630 (amortised)
+            break
+        emb = ops.embed_gather(table.detach(), nxt.view(B, 1))                                      # :634-635
+    stop = min(n, int(all_done_at.item()) + 1)
+    return tokens[:stop].transpose(1, 0).cpu()
+
+
 def _resolve_attachment_idx(attachment_token_idx, tokenizer, attachment_token) -> Optional[int]:
     if attachment_token_idx is not None:
         return int(attachment_token_idx)
@@ -250,6 +304,7 @@ def patch_embed_modalities_with_text(model, attachment_token_idx: Optional[int] 
     model.embed_modalities_with_text = types.MethodType(embed_modalities_with_text, model)
     model.b200_check = b200_check
     model.b200_state = state
+    model.b200_generate = types.MethodType(b200_generate, model)    # device-side decode loop (same signature as generate)
     if not getattr(model, "_b200_generate_wrapped", False):
         ref_generate = model.generate
 

@@ -127,6 +127,32 @@ def test_generate_runs_through_the_plugin(stack):
     print("[ref model] generate:", out.tolist(), "reference bf16 first token:", want.tolist())
 
 
+def test_device_side_generate_is_token_identical_to_the_reference_loop(stack):
+    """integration.b200_generate: the reference's decode loop (model.py:581-638) without the per-token `.cpu()` / Python
+    sampling loop.  Greedy decoding must reproduce `generate` token for token on the SAME model, also when the host only
+    checks the stop condition every few steps, and rows that hit EOS early must be padded with EOS exactly like :620-622."""
+    ref, tok, mb2 = stack["ref"], stack["tok"], stack["mb2"]
+    coll = rh.make_collator(ref, tok, stack["m32"], add_generation_prompt=True)
+    batch = coll(rh.make_samples(stack["imgs"], [1, 2, 0], seed=11))
+    want = mb2.generate(batch, max_new_tokens=12, do_sample=False)
+    for sync_every in (1, 5, 16):
+        got = mb2.b200_generate(batch, max_new_tokens=12, do_sample=False, sync_every=sync_every)
+        assert got.dtype == torch.int64 and not got.is_cuda
+        assert torch.equal(got, want), (sync_every, got.tolist(), want.tolist())
+    # force an early EOS: make the first generated token of row 0 the EOS id and check the tail handling
+    old = mb2.config.eos_token_idx
+    try:
+        mb2.config.eos_token_idx = int(want[0, 0])
+        w2 = mb2.generate(batch, max_new_tokens=8, do_sample=False)
+        g2 = mb2.b200_generate(batch, max_new_tokens=8, do_sample=False, sync_every=3)
+        assert torch.equal(g2, w2), (g2.tolist(), w2.tolist())
+    finally:
+        mb2.config.eos_token_idx = old
+    s = mb2.b200_generate(batch, max_new_tokens=4, do_sample=True, temperature=1.0)
+    assert s.shape == (3, 4) or s.shape[1] <= 4
+    mb2.b200_check()
+
+
 def test_errors_are_the_references_and_do_not_stick(stack):
     mb2, b = stack["mb2"], stack["batch"]
     att = stack["tok"].convert_tokens_to_ids(rh.ATTACHMENT_TOKEN)
