@@ -7,14 +7,14 @@ SMALL="python bench.py --steps 1 --warmup 3 --images-per-gpu 32 --no-cpu-baselin
 FULL="python bench.py --steps 1 --warmup 3 --no-cpu-baseline"
 $SMALL > gpurun_out/plain_small.log 2>&1 &&
 # only this library's kernels are counted (weight packing at load time launches thousands of torch kernels)
-ncu --metrics gpu__time_duration.sum --clock-control none -k "regex:gemm_bf16_tn_kernel|attention_fwd|layernorm_kernel|move_rows|attach_|cls_rows|patch_rows|resize_|weighted_expert" -s 396 -c 140 --csv \
+ncu --metrics gpu__time_duration.sum --clock-control none -k "regex:gemm_bf16_tn_kernel|attention3_fwd|attention_fwd|layernorm_kernel|move_rows|attach_|cls_rows|patch_rows|resize_|weighted_expert" -s 396 -c 140 --csv \
     --log-file gpurun_out/${tag}_launches.csv $SMALL > gpurun_out/ncu_small.log 2>&1
 echo "launch list exit $?"
 $FULL > gpurun_out/plain_full.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:gemm_bf16_tn_kernel -s 320 -c 6 \
     -o gpurun_out/${tag}_gemm $FULL > gpurun_out/ncu_gemm.log 2>&1
 echo "gemm capture exit $?"
-ncu --set full --clock-control none --import-source on -k regex:attention_fwd -s 60 -c 2 \
+ncu --set full --clock-control none --import-source on -k "regex:attention3_fwd|attention_fwd" -s 60 -c 2 \
     -o gpurun_out/${tag}_attn $FULL > gpurun_out/ncu_attn.log 2>&1
 echo "attn capture exit $?"
 ncu --set full --clock-control none --import-source on -k "regex:move_rows_kernel|layernorm_kernel|resize_" -s 6 -c 8 \
