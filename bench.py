@@ -411,9 +411,15 @@ def run_b200(args):
         sd = synth.make_moe_state_dict([cfg] * E, H, False, seed=0, dtype=torch.bfloat16)
         # the reference's gate ON the path (moe/gating.py:73-89: ResNet-50 -> logits -> softmax), random init like the
         # experts; torchvision/cuDNN (library code: SURVEY §8(f) rank 3 keeps it there), bf16 channels-last
-        from multimeditron_b200.gating import ResNet50Gate
+        from multimeditron_b200.gating import B200ResNet50Gate, ResNet50Gate
         torch.manual_seed(7)
-        gate = ResNet50Gate(E, top_k=1, device=dev)
+        tv = ResNet50Gate(E, top_k=1, device="cpu", dtype=torch.float32, fold_bn=False)     # torchvision init = the reference's
+        gsd = {"resnet." + k: v for k, v in tv.resnet.state_dict().items()}
+        if os.environ.get("MM_B200_GATE", "native") == "cudnn":
+            gate = ResNet50Gate(E, top_k=1, device=dev, state_dict=gsd)                      # library path (A/B)
+        else:
+            gate = B200ResNet50Gate(gsd, E, top_k=1, device=dev)                             # every conv on the tcgen05 GEMM
+        del tv
         modality, model_load_s = timed_load(AutoModality.from_config(mcfg), sd, dev, gating=gate)
         # raw mixed-resolution images, packed once (what the collator would hand over), resized on the device
         from multimeditron_b200.preprocess import DevicePreprocessor
@@ -629,9 +635,11 @@ def run_b200(args):
     if E:
         line["config"]["experts"] = E
         line["config"]["inputs"] = "raw uint8 images, sizes drawn from {224,336,512,1024}^2, resized on the device"
-        line["config"]["gating"] = ("reference GatingNetwork on the path: torchvision ResNet-50 (cuDNN, bf16 channels-last) on every "
-                                    "image inside the timed step, overlapping the experts' streams; its FLOPs (~8.2 GFLOP/img) "
-                                    "are NOT credited in path_tensor")
+        line["config"]["gating"] = ("reference GatingNetwork on the path (ResNet-50 on every image inside the timed step, overlapping "
+                                    "the experts' streams): " + ("torchvision on cuDNN, bf16 channels-last"
+                                                                 if os.environ.get("MM_B200_GATE", "native") == "cudnn" else
+                                                                 "native — row staging + tcgen05 GEMMs with BatchNorm/ReLU folded") +
+                                    "; its FLOPs (~8.2 GFLOP/img) are NOT credited in path_tensor")
         line["config"]["expert_streams"] = os.environ.get("MM_B200_MOE_STREAMS", "1") != "0"
         line["gate_ms_standalone"] = gate_ms
     if rank == 0 and world == 1 and not args.no_cpu_baseline and not E:

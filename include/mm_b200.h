@@ -49,6 +49,8 @@ typedef enum mm_act {
   MM_ACT_QUICK_GELU = 1,  /* x*sigmoid(1.702x)   HF:activations.py:117-123 (CLIP MLP)          */
   MM_ACT_GELU_ERF = 2,    /* exact GELU          src/multimeditron/model/projectors/mlp.py:35,37 */
   MM_ACT_GELU_TANH = 3,   /* gelu_pytorch_tanh   HF:models/siglip (hidden_act)                 */
+  MM_ACT_RELU = 4,        /* max(x, 0) applied LAST, i.e. AFTER the optional residual add: relu(bf16(acc+bias) + res) —
+                             torchvision Bottleneck (`out += identity; out = relu(out)`), the MoE gate's ResNet-50   */
   /* per-call tuning flag OR-ed into `act` of mm_gemm_bias_act / mm_gemm_ln_bias_act: run the 1-CTA kernel
    * (128 x 256 tiles) instead of the default CTA-pair kernel (tcgen05 cta_group::2, 256 x 256 tiles, M > 128).
    * Both kernels accumulate every output in the same k order: results are bit-identical (tested).            */
@@ -252,6 +254,23 @@ int mm_attention_fwd(const void* qkv, void* out, int64_t B, int64_t T, int64_t h
  */
 int mm_weighted_expert_sum(const void* x, const float* w, const int32_t* perm, void* out,
                            int64_t E, int64_t B, int64_t P, int64_t D, void* stream);
+
+/*
+ * Row staging and pooling for the MoE gate's ResNet-50 (src/multimeditron/model/modalities/moe/gating.py:60-65,85 —
+ * torchvision resnet50).  Every convolution runs as mm_gemm_bias_act on NHWC activations
+ * ([B*H*W, C] bf16), BatchNorm folded into weight/bias at load time, MM_ACT_RELU in the epilogue.
+ *   mm_conv_rows_nhwc : x [B,H,W,C] bf16 -> out [B*Ho*Wo, Kpad] bf16, k = (ky*kw + kx)*C + c, zeros outside the image
+ *                       and in the K padding; Ho = (H + 2*pad - kh)/stride + 1 (3x3 and strided 1x1 convolutions)
+ *   mm_conv_rows_stem : x [B,3,H,W] fp32|bf16 (NCHW pixel_values) -> out [B*Ho*Wo, Kpad], k = (ky*kw + kx)*3 + c
+ *   mm_maxpool_nhwc   : 3x3, stride 2, pad 1 (-inf padding), bf16 [B,H,W,C] -> [B,Ho,Wo,C]
+ *   mm_avgpool_nhwc   : mean over the HW pixels, fp32 accumulation: [B,HW,C] -> [B,C] bf16
+ */
+int mm_conv_rows_nhwc(const void* x, void* out, int64_t B, int64_t H, int64_t W, int64_t C, int64_t kh, int64_t kw,
+                      int64_t stride, int64_t pad, int64_t Kpad, void* stream);
+int mm_conv_rows_stem(const void* x, int x_dtype, void* out, int64_t B, int64_t H, int64_t W, int64_t kh, int64_t kw,
+                      int64_t stride, int64_t pad, int64_t Kpad, void* stream);
+int mm_maxpool_nhwc(const void* x, void* out, int64_t B, int64_t H, int64_t W, int64_t C, void* stream);
+int mm_avgpool_nhwc(const void* x, void* out, int64_t B, int64_t HW, int64_t C, void* stream);
 
 /*
  * mm_cross_attention — the MoE 'cross_attn' fusion's attention: generalist queries over the

@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA, kPair>::kThreads, 1)
             const uint64_t x2 = fold ? fma_f32x2(rstd2, a2, b2) : add_f32x2(a2, b2);  // fold: rstd*(x·W''ᵀ) + b'
             float x0, x1;
             f32x2_unpack(x2, x0, x1);
-            if (ACT != MM_ACT_NONE) {
+            if (ACT != MM_ACT_NONE && ACT != MM_ACT_RELU) {   // (ReLU is applied last, after the residual)
               const uint32_t r = pack_bf16x2(x0, x1);
               x0 = apply_act<ACT>(bf16_lo(r));
               x1 = apply_act<ACT>(bf16_hi(r));
@@ -386,6 +386,12 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA, kPair>::kThreads, 1)
               v.y = add_bf16x2(v.y, (uint32_t)rv[it].y);
               v.z = add_bf16x2(v.z, (uint32_t)rv[it].z);
               v.w = add_bf16x2(v.w, (uint32_t)rv[it].w);
+            }
+            if (ACT == MM_ACT_RELU) {   // relu(bf16(acc + bias) [+ res]): packed bf16 max against +0
+              asm("max.bf16x2 %0, %0, %1;" : "+r"(v.x) : "r"(0u));
+              asm("max.bf16x2 %0, %0, %1;" : "+r"(v.y) : "r"(0u));
+              asm("max.bf16x2 %0, %0, %1;" : "+r"(v.z) : "r"(0u));
+              asm("max.bf16x2 %0, %0, %1;" : "+r"(v.w) : "r"(0u));
             }
             *reinterpret_cast<uint4*>(p.C + (int64_t)out_rows[it] * p.ldc + col) = v;
             if (want_stats) {  // statistics of the values as stored (bf16-rounded), fp32, two lanes per instruction
@@ -715,6 +721,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParam
     case MM_ACT_QUICK_GELU: return launch_gemm_inst<false, MM_ACT_QUICK_GELU>(tmA, tmB, p, st);
     case MM_ACT_GELU_ERF: return launch_gemm_inst<false, MM_ACT_GELU_ERF>(tmA, tmB, p, st);
     case MM_ACT_GELU_TANH: return launch_gemm_inst<false, MM_ACT_GELU_TANH>(tmA, tmB, p, st);
+    case MM_ACT_RELU: return launch_gemm_inst<false, MM_ACT_RELU>(tmA, tmB, p, st);
   }
   return MM_ERR_BAD_ARG;
 }
@@ -738,7 +745,7 @@ static int gemm_entry(const void* A, int64_t lda, const void* W, int64_t ldw, co
     return MM_ERR_BAD_ARG;
   const bool force_1cta = (act & MM_GEMM_FLAG_1CTA) != 0;
   act &= ~MM_GEMM_FLAG_1CTA;
-  if (act < MM_ACT_NONE || act > MM_ACT_GELU_TANH) return MM_ERR_BAD_ARG;
+  if (act < MM_ACT_NONE || act > MM_ACT_RELU) return MM_ERR_BAD_ARG;
   if (out_row_map && n_out_rows <= 0) return MM_ERR_BAD_ARG;
   CUtensorMap tmA, tmB;
   int rc = make_tmap_2d(&tmA, A, M, K, lda, BM);

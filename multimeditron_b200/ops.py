@@ -10,7 +10,7 @@ import torch
 from . import _lib
 
 MM_BF16, MM_F32 = 0, 1
-ACT_NONE, ACT_QUICK_GELU, ACT_GELU_ERF, ACT_GELU_TANH = 0, 1, 2, 3
+ACT_NONE, ACT_QUICK_GELU, ACT_GELU_ERF, ACT_GELU_TANH, ACT_RELU = 0, 1, 2, 3, 4
 ACT_BY_NAME = {
     None: ACT_NONE, "none": ACT_NONE, "quick_gelu": ACT_QUICK_GELU, "gelu": ACT_GELU_ERF,
     "gelu_pytorch_tanh": ACT_GELU_TANH, "gelu_tanh": ACT_GELU_TANH,
@@ -393,6 +393,60 @@ def weighted_expert_sum(x: torch.Tensor, w: torch.Tensor, perm: torch.Tensor | N
     with _timed("mm_weighted_expert_sum", 2.0 * (E + 1) * R * D):
         rc = lib.mm_weighted_expert_sum(_ptr(x), _ptr(w), _ptr(perm), _ptr(out), E, B, P, D, _stream())
     _check(rc, "mm_weighted_expert_sum")
+    return out
+
+
+# --------------------------------------------------------------------------------- ResNet gate: row staging / pooling
+def conv_out_size(n: int, k: int, stride: int, pad: int) -> int:
+    return (n + 2 * pad - k) // stride + 1
+
+
+def conv_rows_nhwc(x: torch.Tensor, kh: int, kw: int, stride: int, pad: int, kpad: int) -> torch.Tensor:
+    """x [B,H,W,C] bf16 -> [B*Ho*Wo, kpad] bf16 rows of a kh x kw convolution (k = (ky*kw+kx)*C + c)."""
+    _cuda(x)
+    B, H, W, Cc = x.shape
+    assert x.dtype == torch.bfloat16 and x.is_contiguous()
+    Ho, Wo = conv_out_size(H, kh, stride, pad), conv_out_size(W, kw, stride, pad)
+    out = torch.empty(B * Ho * Wo, kpad, dtype=torch.bfloat16, device=x.device)
+    with _timed("mm_conv_rows", 2.0 * out.numel() * 2):
+        rc = _lib.load().mm_conv_rows_nhwc(_ptr(x), _ptr(out), B, H, W, Cc, kh, kw, stride, pad, kpad, _stream())
+    _check(rc, "mm_conv_rows_nhwc")
+    return out
+
+
+def conv_rows_stem(x: torch.Tensor, kh: int, kw: int, stride: int, pad: int, kpad: int) -> torch.Tensor:
+    """x [B,3,H,W] fp32|bf16 (pixel_values) -> [B*Ho*Wo, kpad] bf16 rows of the stem convolution."""
+    _cuda(x)
+    B, Cc, H, W = x.shape
+    assert Cc == 3 and x.is_contiguous()
+    Ho, Wo = conv_out_size(H, kh, stride, pad), conv_out_size(W, kw, stride, pad)
+    out = torch.empty(B * Ho * Wo, kpad, dtype=torch.bfloat16, device=x.device)
+    with _timed("mm_conv_rows", float(x.numel() * x.element_size() + out.numel() * 2)):
+        rc = _lib.load().mm_conv_rows_stem(_ptr(x), _dt(x), _ptr(out), B, H, W, kh, kw, stride, pad, kpad, _stream())
+    _check(rc, "mm_conv_rows_stem")
+    return out
+
+
+def maxpool_nhwc(x: torch.Tensor) -> torch.Tensor:
+    _cuda(x)
+    B, H, W, Cc = x.shape
+    assert x.dtype == torch.bfloat16 and x.is_contiguous()
+    out = torch.empty(B, conv_out_size(H, 3, 2, 1), conv_out_size(W, 3, 2, 1), Cc, dtype=torch.bfloat16, device=x.device)
+    with _timed("mm_pool", float(x.numel() * 2 + out.numel() * 2)):
+        rc = _lib.load().mm_maxpool_nhwc(_ptr(x), _ptr(out), B, H, W, Cc, _stream())
+    _check(rc, "mm_maxpool_nhwc")
+    return out
+
+
+def avgpool_nhwc(x: torch.Tensor) -> torch.Tensor:
+    """[B,HW,C] bf16 -> [B,C] bf16."""
+    _cuda(x)
+    B, HW, Cc = x.shape
+    assert x.dtype == torch.bfloat16 and x.is_contiguous()
+    out = torch.empty(B, Cc, dtype=torch.bfloat16, device=x.device)
+    with _timed("mm_pool", float(x.numel() * 2)):
+        rc = _lib.load().mm_avgpool_nhwc(_ptr(x), _ptr(out), B, HW, Cc, _stream())
+    _check(rc, "mm_avgpool_nhwc")
     return out
 
 

@@ -107,3 +107,69 @@ def test_resnet50_gate_matches_the_reference_gating_network():
     assert torch.allclose(w.float().sum(-1), torch.ones(6, device=DEV), atol=2e-2)
     scale = l32.abs().max().item()
     assert (l.float() - l32).abs().max().item() <= 5e-2 * scale
+
+
+@pytest.mark.parametrize("size", [224, 96])
+def test_native_resnet50_gate_vs_torchvision_fp32(size):
+    """gating.B200ResNet50Gate: the reference gate's ResNet-50 with every convolution on the tcgen05 GEMM (row staging,
+    BatchNorm folded, ReLU / add-then-ReLU epilogues, NHWC activations) against torchvision's own forward in fp32 — and
+    against torchvision in bf16 on cuDNN (the reference's regime) for scale: the native path must not be further from
+    fp32 than 2x what cuDNN's bf16 run is."""
+    pytest.importorskip("torchvision")
+    from multimeditron_b200.gating import B200ResNet50Gate, ResNet50Gate
+    torch.manual_seed(5)
+    ref = ResNet50Gate(5, top_k=2, device=DEV, dtype=torch.float32, fold_bn=False)
+    for m in ref.resnet.modules():
+        if isinstance(m, torch.nn.BatchNorm2d):
+            m.running_mean.normal_(0, 0.1); m.running_var.uniform_(0.5, 1.5)
+            m.weight.data.uniform_(0.5, 1.5); m.bias.data.normal_(0, 0.1)
+    sd = {"gating_network.resnet." + k: v for k, v in ref.resnet.state_dict().items()}
+    gate = B200ResNet50Gate(sd, 5, top_k=2, device=DEV, prefix="gating_network.resnet.")
+    lib16 = ResNet50Gate(5, top_k=2, device=DEV, state_dict=sd, prefix="gating_network.resnet.", fold_bn=False)
+    px = torch.randn(6, 3, size, size, device=DEV)
+    l32, t32, w32 = ref(px)
+    l, t, w = gate(px)
+    lb, _, _ = lib16(px.bfloat16())
+    assert l.shape == (6, 5) and w.shape == (6, 5) and t.shape == (6, 2)
+    scale = l32.abs().max().item()
+    err, lib_err = (l.float() - l32).abs().max().item(), (lb.float() - l32).abs().max().item()
+    print(f"[native gate {size}px] logits max-abs {err:.3e} (torchvision bf16 on cuDNN: {lib_err:.3e}) of scale {scale:.3e}; "
+          f"weights max-abs {(w.float() - w32).abs().max().item():.3e}")
+    assert err <= 2.0 * lib_err + 1e-2 * scale
+    assert torch.allclose(w.float().sum(-1), torch.ones(6, device=DEV), atol=2e-2)
+    lp, _, _ = gate(px.bfloat16())                    # bf16 pixels (what the device pre-processor hands over)
+    assert (lp.float() - l32).abs().max().item() <= 2.0 * lib_err + 2e-2 * scale
+
+
+def test_conv_rows_and_pools_bit_exact():
+    """mm_conv_rows_nhwc / _stem, mm_maxpool_nhwc, mm_avgpool_nhwc against torch (unfold / max_pool2d / mean)."""
+    from multimeditron_b200 import ops
+    import torch.nn.functional as F
+    g0 = torch.Generator().manual_seed(1)
+    x = torch.randn(3, 10, 13, 16, generator=g0).bfloat16().to(DEV)                    # NHWC
+    for (k, s, p) in ((3, 1, 1), (3, 2, 1), (1, 2, 0)):
+        kpad = (k * k * 16 + 63) // 64 * 64
+        rows = ops.conv_rows_nhwc(x, k, k, s, p, kpad)
+        unf = F.unfold(x.permute(0, 3, 1, 2).float(), k, padding=p, stride=s)           # [B, C*k*k, L], (c, ky, kx) order
+        L = unf.shape[-1]
+        want = unf.view(3, 16, k * k, L).permute(0, 3, 2, 1).reshape(3 * L, k * k * 16)   # -> (ky,kx,c) order
+        assert torch.equal(rows[:, :k * k * 16].float(), want) and not rows[:, k * k * 16:].any()
+    px = torch.randn(2, 3, 20, 23, generator=g0).to(DEV)
+    rows = ops.conv_rows_stem(px, 7, 7, 2, 3, 192)
+    unf = F.unfold(px, 7, padding=3, stride=2)
+    L = unf.shape[-1]
+    want = unf.view(2, 3, 49, L).permute(0, 3, 2, 1).reshape(2 * L, 147).bfloat16()
+    assert torch.equal(rows[:, :147], want) and not rows[:, 147:].any()
+    mp = ops.maxpool_nhwc(x)
+    assert torch.equal(mp.permute(0, 3, 1, 2).float(), F.max_pool2d(x.permute(0, 3, 1, 2).float(), 3, 2, 1))
+    ap = ops.avgpool_nhwc(x.view(3, 130, 16))
+    assert torch.equal(ap, x.view(3, 130, 16).float().mean(1).bfloat16())
+    # ReLU epilogue applied AFTER the residual add
+    a = torch.randn(300, 64, generator=g0).bfloat16().to(DEV)
+    w = (torch.randn(64, 64, generator=g0) * 0.2).bfloat16().to(DEV)
+    b = torch.randn(64, generator=g0).bfloat16().to(DEV)
+    r = torch.randn(300, 64, generator=g0).bfloat16().to(DEV)
+    got = ops.gemm_bias_act(a, w, b, act=ops.ACT_RELU, residual=r)
+    lin = ops.gemm_bias_act(a, w, b)
+    assert torch.equal(got, torch.relu((lin.float() + r.float()).bfloat16()))
+    assert torch.equal(ops.gemm_bias_act(a, w, b, act=ops.ACT_RELU), torch.relu(lin))
