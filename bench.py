@@ -45,9 +45,9 @@ GLOBAL_BATCH = {"cfg1_clip_b32_tiny_llama": 8, "cfg2_clip_l14_336_llama8b": 256,
                 "cfg4_interleaved_8k": 256, "cfg5_moe_5x_clip_b32_llama8b": 256}
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` capture of this command at
-# cfg2 B=256 (profiles/r01h_ncu_full_summary.txt): GEMM = mean over one encoder layer's four launches
-# (fc2+stats 1.818, qkv(LN folded) 1.182, out-proj+stats 0.877, fc1(LN folded) 1.487 GB).
-NCU_TRAFFIC = {"cfg2_clip_l14_336_llama8b": {"gemm": 1.386e9, "attention": 1.1849e9, "layernorm": 0.5464e9}}
+# cfg2 B=256 (profiles/r02_ncu_full_summary.txt, round 2 code): GEMM = mean over one encoder layer's four launches
+# (fc2+stats 1.847, qkv(LN folded) 1.184, out-proj+stats 0.883, fc1(LN folded) 1.486 GB); attention3 1.183 GB.
+NCU_TRAFFIC = {"cfg2_clip_l14_336_llama8b": {"gemm": 1.350e9, "attention": 1.1833e9, "layernorm": 0.5464e9}}
 
 
 def workload(wl):
@@ -508,8 +508,13 @@ def run_b200(args):
     ms = timed(step_dev, args.steps)                # `value`: no per-op instrumentation in this region
     launches_per_step = ops.LAUNCHES // args.steps
     ops.profile_start()                             # second timed region of the same K steps with one CUDA-event pair per
-    ms_profiled = timed(step_dev, args.steps)       # op on the launching stream: per-kernel durations for the rooflines
+    if E:                                           # op on the launching stream: per-kernel durations for the rooflines
+        os.environ["MM_B200_MOE_STREAMS_SAVED"] = os.environ.get("MM_B200_MOE_STREAMS", "1")
+        os.environ["MM_B200_MOE_STREAMS"] = "0"     # (experts serialised here: concurrent streams would overlap the events)
+    ms_profiled = timed(step_dev, args.steps)
     prof = ops.profile_stop()
+    if E:
+        os.environ["MM_B200_MOE_STREAMS"] = os.environ.pop("MM_B200_MOE_STREAMS_SAVED")
     # ---- optional: the same step replayed from ONE CUDA graph (launch-bound workloads: cfg1 is 132 launches for
     # ~0.1 ms of math).  Captured after warm-up, so every one-time attribute / workspace allocation already happened;
     # the graph's private pool keeps every pointer baked into a tensor map stable across replays.
@@ -619,7 +624,7 @@ def run_b200(args):
                      "frac": gemm_tf / pk["tf_sust"],
                      "traffic": NCU_TRAFFIC.get(args.workload, {}).get("gemm") if images == w["images"] else None,
                      "traffic_src": "ncu --set full, mean bytes per launch over one encoder layer's 4 GEMMs "
-                                    "(profiles/r01k_ncu_full_summary.txt)",
+                                    "(profiles/r02_ncu_full_summary.txt)",
                      "peak_kind": f"{pk['src']} sustained cuBLAS bf16 (kernel timed inside a long step)",
                      "frac_of_burst": gemm_tf / pk["tf_burst"]},
         "path_tensor": {"achieved": path_tf, "unit": "TFLOP/s", "frac_of_sustained": path_tf / pk["tf_sust"],
