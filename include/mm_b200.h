@@ -201,6 +201,19 @@ int mm_gemm_ln_bias_act(const void* A, int64_t lda, const void* W, int64_t ldw, 
                         const void* residual, int64_t ldr, const int32_t* out_row_map,
                         int64_t n_out_rows, void* stats_out, const void* ln_stats, float ln_eps,
                         void* stream);
+/*
+ * mm_gemm_grouped — `groups` GEMMs of IDENTICAL shape in one persistent launch (the MoE modalities' experts:
+ * image_modality_moe.py:160-162 runs every expert tower on every image, one after the other).  Everything is stacked:
+ *   A [groups*M, K], C / residual [groups*M, N], stats [groups*M, slots] along the rows; W [groups*N, K] and bias
+ *   [groups*N] along the rows of W.  Row tile r multiplies the weight block of group r / (M / tile_rows); M must be a
+ *   multiple of the row tile (256 for the CTA-pair kernel, 128 with MM_GEMM_FLAG_1CTA), so no tile straddles two groups.
+ * One launch walks groups*tiles tiles round-robin over the CTA pairs: 5 experts x 150 tiles fill 10.1 waves instead of
+ * 5 x 2.03.  Options as mm_gemm_ln_bias_act (act, residual, out_row_map over the stacked rows, stats_out, ln_stats).
+ */
+int mm_gemm_grouped(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias, void* C, int64_t ldc,
+                    int64_t M, int64_t N, int64_t K, int64_t groups, int act, const void* residual, int64_t ldr,
+                    const int32_t* out_row_map, int64_t n_out_rows, void* stats_out, const void* ln_stats,
+                    float ln_eps, void* stream);
 
 /*
  * mm_patch_embed — im2col-free implicit GEMM of the patch convolution

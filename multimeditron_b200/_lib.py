@@ -47,6 +47,7 @@ SIGNATURES = {
     "mm_attention_head_stride": (i64, [i64]),
     "mm_attention_fwd": (i32, [vp, vp, i64, i64, i64, i64, f32, vp]),
     "mm_weighted_expert_sum": (i32, [vp, vp, vp, vp, i64, i64, i64, i64, vp]),
+    "mm_gemm_grouped": (i32, [vp, i64, vp, i64, vp, vp, i64, i64, i64, i64, i64, i32, vp, i64, vp, i64, vp, vp, f32, vp]),
     "mm_conv_rows_nhwc": (i32, [vp, vp, i64, i64, i64, i64, i64, i64, i64, i64, i64, vp]),
     "mm_conv_rows_stem": (i32, [vp, i32, vp, i64, i64, i64, i64, i64, i64, i64, i64, vp]),
     "mm_maxpool_nhwc": (i32, [vp, vp, i64, i64, i64, i64, vp]),

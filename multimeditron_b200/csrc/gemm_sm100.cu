@@ -77,6 +77,10 @@ struct GemmParams {
   int act;
   int tiles_m, tiles_n;
   int pair;  // 1: CTA-pair kernel (256-row tiles; the B tensor map has a 128-row box)
+  // grouped launch (mm_gemm_grouped): `groups` problems of identical shape stacked along the rows of A / C / residual /
+  // statistics and along the rows of W (and bias).  Row tile r belongs to group r / group_tiles_m and multiplies the
+  // W rows [group * group_n, +N).  0 = one problem.
+  int group_tiles_m, group_n;
   // LayerNorm folded into the GEMM (mm_gemm_ln_bias_act):  LN(x)·Wᵀ + b = rstd·(x·W''ᵀ) + b'
   // with W'' = gamma ⊙ W re-centred so that every row sums to zero (the mean term cancels inside the MMA).
   //   producer side: per 64-column chunk (sum, sum of squares) of the rows this GEMM writes
@@ -190,7 +194,9 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA, kPair>::kThreads, 1)
       int stage = 0;
       uint32_t phase = 0;
       for (int t = tile0; t < num_tiles; t += tile_step) {
-        const int m0 = (t / p.tiles_n) * kTileRows + m_off, n0 = (t % p.tiles_n) * BN + (kPair ? m_off : 0);
+        const int grp = p.group_tiles_m ? (t / p.tiles_n) / p.group_tiles_m : 0;
+        const int m0 = (t / p.tiles_n) * kTileRows + m_off;
+        const int n0 = (t % p.tiles_n) * BN + (kPair ? m_off : 0) + grp * p.group_n;   // row of the (stacked) W
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&tail->empty[stage], phase ^ 1);
           if (kPair) {
@@ -276,6 +282,8 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA, kPair>::kThreads, 1)
     if (fold_mode) load_stats(tile0);
     for (int t = tile0; t < num_tiles; t += tile_step) {
       const int m0 = (t / p.tiles_n) * kTileRows + m_off, n0 = (t % p.tiles_n) * BN;
+      const __nv_bfloat16* bias_g = p.bias;
+      if (p.bias && p.group_tiles_m) bias_g += (size_t)((t / p.tiles_n) / p.group_tiles_m) * p.group_n;
       // destination row of this lane's GEMM row
       const int my_m = m0 + q * 32 + lane;
       int my_out = -1;
@@ -327,7 +335,7 @@ __global__ void __launch_bounds__(GemmCfg<kGatherA, kPair>::kThreads, 1)
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           bv[j] = make_int4(0, 0, 0, 0);
-          if (p.bias && col0 + j * 8 < p.N) bv[j] = __ldg(reinterpret_cast<const int4*>(p.bias + col0 + j * 8));
+          if (p.bias && col0 + j * 8 < p.N) bv[j] = __ldg(reinterpret_cast<const int4*>(bias_g + col0 + j * 8));
         }
         const int ch = lane & 7;
         const int col = col0 + ch * 8;
@@ -735,8 +743,11 @@ static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 static int gemm_entry(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias, void* C, int64_t ldc,
                       int64_t M, int64_t N, int64_t K, int act, const void* residual, int64_t ldr, int64_t res_mod,
                       int64_t res_row_off, const int32_t* out_row_map, int64_t n_out_rows, void* stats_out,
-                      const void* ln_stats, float ln_eps, void* stream) {
-  if (M < 0 || N <= 0 || K <= 0 || M > INT32_MAX / 2 || N > INT32_MAX / 2 || K > INT32_MAX / 2) return MM_ERR_BAD_ARG;
+                      const void* ln_stats, float ln_eps, void* stream, int64_t groups = 1) {
+  if (groups < 1 || groups > 64) return MM_ERR_BAD_ARG;
+  const int64_t Mg = M;          // rows per group
+  M *= groups;                   // rows of the stacked problem
+  if (M < 0 || N <= 0 || K <= 0 || M > INT32_MAX / 2 || N * groups > INT32_MAX / 2 || K > INT32_MAX / 2) return MM_ERR_BAD_ARG;
   if (M == 0) return MM_OK;
   if (!A || !W || !C) return MM_ERR_BAD_ARG;
   if (K % 8 || N % 8 || lda % 8 || ldw % 8 || ldc % 8 || (residual && ldr % 8)) return MM_ERR_BAD_ARG;
@@ -751,10 +762,13 @@ static int gemm_entry(const void* A, int64_t lda, const void* W, int64_t ldw, co
   int rc = make_tmap_2d(&tmA, A, M, K, lda, BM);
   if (rc != MM_OK) return rc;
   const bool pair = M > BM && !force_1cta && pair_enabled();   // at most one row tile: the peer CTA would only see padding
-  rc = make_tmap_2d(&tmB, W, N, K, ldw, pair ? BN / 2 : BN);
+  if (groups > 1 && (Mg % (pair ? 2 * BM : BM) || res_mod > 0)) return MM_ERR_BAD_ARG;   // a row tile must not straddle two groups
+  rc = make_tmap_2d(&tmB, W, N * groups, K, ldw, pair ? BN / 2 : BN);
   if (rc != MM_OK) return rc;
   GemmParams p{};
   p.pair = pair ? 1 : 0;
+  p.group_tiles_m = groups > 1 ? (int)(Mg / (pair ? 2 * BM : BM)) : 0;
+  p.group_n = (int)N;
   p.C = reinterpret_cast<__nv_bfloat16*>(C);
   p.bias = reinterpret_cast<const __nv_bfloat16*>(bias);
   p.residual = reinterpret_cast<const __nv_bfloat16*>(residual);
@@ -782,6 +796,14 @@ extern "C" int mm_gemm_bias_act(const void* A, int64_t lda, const void* W, int64
                                 int64_t n_out_rows, void* stream) {
   return gemm_entry(A, lda, W, ldw, bias, C, ldc, M, N, K, act, residual, ldr, res_mod, res_row_off, out_row_map,
                     n_out_rows, nullptr, nullptr, 0.f, stream);
+}
+
+extern "C" int mm_gemm_grouped(const void* A, int64_t lda, const void* W, int64_t ldw, const void* bias, void* C, int64_t ldc,
+                               int64_t M, int64_t N, int64_t K, int64_t groups, int act, const void* residual, int64_t ldr,
+                               const int32_t* out_row_map, int64_t n_out_rows, void* stats_out, const void* ln_stats,
+                               float ln_eps, void* stream) {
+  return gemm_entry(A, lda, W, ldw, bias, C, ldc, M, N, K, act, residual, ldr, 0, 0, out_row_map, n_out_rows, stats_out,
+                    ln_stats, ln_eps, stream, groups);
 }
 
 extern "C" int64_t mm_gemm_row_stats_slots(int64_t N) { return (N > 0 && N <= 128 * kStatSlots) ? kStatSlots : -1; }

@@ -558,12 +558,15 @@ __global__ void __launch_bounds__(kPosThreads) position_ids_kernel(const int64_t
   const MaskT* rm = mask + (int64_t)b * S;
   const int chunk = (S + kPosThreads - 1) / kPosThreads;
   const int c0 = min(threadIdx.x * chunk, S), c1 = min(c0 + chunk, S);
-  int n_mask = 0, n_start = 0;
+  // An image starts at every P-th attachment token of the row — the reference's own rule (compute_token_range,
+  // prompt_tokenizers.py:255-286: "the k-th modality starts at the (sum of the previous lengths)-th attachment token"),
+  // so two images that touch without delimiters are still two images.
+  int n_mask = 0, n_att = 0;
   for (int t = c0; t < c1; ++t) {
     n_mask += rm[t] != 0;
-    if (use_2d) n_start += (rid[t] == att) && (t == 0 || rid[t - 1] != att);
+    if (use_2d) n_att += rid[t] == att;
   }
-  int tot_mask, tot_start = 0;
+  int tot_mask, tot_start = 0, tot_att = 0;
   const int pre_mask = block_exclusive_scan(n_mask, warp_sums, tot_mask);
   if (!use_2d) {
     int run = pre_mask;
@@ -574,15 +577,24 @@ __global__ void __launch_bounds__(kPosThreads) position_ids_kernel(const int64_t
     }
     return;
   }
+  __syncthreads();
+  const int pre_att = block_exclusive_scan(n_att, warp_sums, tot_att);
+  int n_start = 0;
+  {
+    int a = pre_att;
+    for (int t = c0; t < c1; ++t)
+      if (rid[t] == att) n_start += (a++ % P) == 0;
+  }
+  __syncthreads();
   const int pre_start = block_exclusive_scan(n_start, warp_sums, tot_start);
   int64_t* ro = out + (int64_t)b * S * 2;
   {  // pass 1: 1-D ids (kept in component 0 for the serial pass) and the ordered list of image starts
-    int run = pre_mask, k = pre_start;
+    int run = pre_mask, k = pre_start, a = pre_att;
     for (int t = c0; t < c1; ++t) {
       const bool m = rm[t] != 0;
       run += m;
       ro[2 * (int64_t)t] = m ? run - 1 : 0;
-      if ((rid[t] == att) && (t == 0 || rid[t - 1] != att)) {
+      if (rid[t] == att && (a++ % P) == 0) {
         if (k < kPosMaxImages) s_start[k] = t;
         ++k;
       }

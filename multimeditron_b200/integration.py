@@ -251,7 +251,10 @@ def patch_embed_modalities_with_text(model, attachment_token_idx: Optional[int] 
                 if want != have:                                                     # index_put_, model.py:441
                     raise RuntimeError(f"shape mismatch: value tensor of shape [{want}, {H}] cannot be broadcast to "
                                        f"indexing result of shape [{have}, {H}]")
-        ids = input_ids.to(dev, non_blocking=True)
+        if state.get("stager") is None or state["stager"].device != dev:
+            from .h2d import HostTensorStager
+            state["stager"] = HostTensorStager(dev)
+        ids = state["stager"].upload(input_ids)             # pageable host ids -> pinned staging -> async H2D
         if state["status"] is None or state["status"].device != dev:
             state["status"] = ops.new_status(dev)
         st = state["status"]
@@ -280,8 +283,8 @@ def patch_embed_modalities_with_text(model, attachment_token_idx: Optional[int] 
                     ops.splice_scatter(embedded.view(B * S, H), src.contiguous(), dest_rows, status=st)
             else:
                 proj = modality(stack)
-                bi = processed_multimodal_inputs["batch_idx"][modality_name].to(dev, non_blocking=True)
-                tr = processed_multimodal_inputs["token_range"][modality_name].to(dev, non_blocking=True)
+                bi = state["stager"].upload(processed_multimodal_inputs["batch_idx"][modality_name])
+                tr = state["stager"].upload(processed_multimodal_inputs["token_range"][modality_name])
                 src = proj.reshape(-1, H).to(embedded.dtype)
                 if proj.requires_grad:
                     from .autograd_ops import splice_rows

@@ -24,7 +24,7 @@ from .. import ops
 from ..configs import TOWERS, TowerConfig
 from ..h2d import H2DUploader
 from ..preprocess import DevicePreprocessor, PackedImages
-from ..vit import ProjectorWeights, TowerRunner, TowerWeights
+from ..vit import FOLD_LN, GroupedTowerRunner, ProjectorWeights, TowerRunner, TowerWeights
 from .base import AutoModality, BaseModality, BaseModalityConfig, BaseModalityProcessor
 from .constants import MODALITY_VALUE_KEY, NUM_EMBEDDINGS_KEY
 from .image_modality import resolve_tower
@@ -165,6 +165,13 @@ class _B200MOEBase(BaseModality):
         else:
             self._projs = [ProjectorWeights(sd, dev, "projector.")]
         self._device = dev
+        # same-shaped experts: one grouped launch per layer op for all of them (vit.GroupedTowerRunner); used whenever
+        # the batch allows it (B*T % 256 == 0), the per-expert runners otherwise.  MM_B200_MOE_GROUPED=0: A/B switch.
+        import os
+        self._grouped = None
+        if (len(self.towers) > 1 and all(t == self.towers[0] for t in self.towers) and FOLD_LN
+                and os.environ.get("MM_B200_MOE_GROUPED", "1") != "0"):
+            self._grouped = GroupedTowerRunner([r.w for r in self._runners])
         self._perm = torch.tensor(self._perm_list, dtype=torch.int32, device=dev)
         self._xattn = None
         if self.fusion_method == "cross_attn":    # CrossAttention parameters (attention.py:36-42), k|v fused into one GEMM
@@ -279,6 +286,35 @@ class _B200MOEBase(BaseModality):
         a = ops.cross_attention(q.view(B, P, C), kv, self.config.cross_attn_heads)
         return ops.gemm_bias_act(a.view(B * P, C), xa["wo"], xa["bo"])
 
+    def _experts_and_gate(self, px: torch.Tensor, stack: torch.Tensor) -> torch.Tensor:
+        """stack[e] = expert e's CLS-dropped features [B*P, D] (image_modality_moe.py:160-162); returns the gate's
+        weights [B,E] (:156).  Same-shaped experts and an eligible batch: ONE grouped launch per layer op on the current
+        stream, the gate on a side stream next to it; otherwise one stream per expert and the gate on the current one."""
+        if self._grouped is not None and self._grouped.eligible(px.shape[0]):
+            import os
+            if os.environ.get("MM_B200_MOE_STREAMS", "1") == "0":      # A/B and per-op profiling: everything on one stream
+                self._grouped.features(px, stack)
+                self._joins = None
+                return self._weights(px)
+            cur = torch.cuda.current_stream(self._device)
+            if getattr(self, "_gate_stream", None) is None:
+                self._gate_stream = torch.cuda.Stream(device=self._device)
+            fork = torch.cuda.Event()
+            fork.record(cur)
+            self._gate_stream.wait_event(fork)
+            with torch.cuda.stream(self._gate_stream):
+                w = self._weights(px)
+                done = torch.cuda.Event()
+                done.record(self._gate_stream)
+            self._grouped.features(px, stack)
+            cur.wait_event(done)
+            self._joins = None
+            return w
+        self._each_expert(lambda e, r: r.features(px, out=stack[e]))
+        w = self._weights(px)
+        self._join_experts()
+        return w
+
     def _each_expert(self, fn):
         """Run fn(e, runner) for every expert, expert e on its own CUDA stream (fork from / join into the current
         stream).  Each expert's GEMMs are persistent kernels with a short tail wave (cfg5: 150 tiles on 74 CTA pairs =
@@ -338,15 +374,11 @@ class B200MOEImageModality(_B200MOEBase):
         r0, proj = self._runners[0], self._projs[0]
         if self.fusion_method == "weighted_average":
             stack = torch.empty(E, B * P, D, dtype=torch.bfloat16, device=self._device)
-            self._each_expert(lambda e, r: r.features(px, out=stack[e]))           # :160-162 (every expert)
-            w = self._weights(px)                                                  # :156 (overlaps the experts)
-            self._join_experts()
+            w = self._experts_and_gate(px, stack)                                  # :156, :160-162 (every expert)
             fused = ops.weighted_expert_sum(stack, w, self._perm, B, P)            # :171-177 (permuted weights)
         elif self.fusion_method == "cross_attn":                                   # :178-205
             stack = torch.empty(E, B * P, D, dtype=torch.bfloat16, device=self._device)
-            self._each_expert(lambda e, r: r.features(px, out=stack[e]))
-            w = self._weights(px)
-            self._join_experts()
+            w = self._experts_and_gate(px, stack)
             fused = self._cross_attn_fuse(stack, w, B, P)
         else:                                                                      # sequence_append :167-169
             fused = torch.empty(B * E * P, D, dtype=torch.bfloat16, device=self._device)

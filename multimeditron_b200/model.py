@@ -48,6 +48,12 @@ class B200MultiModalEmbedder(torch.nn.Module):
             raise TypeError(f"Registered modality {name} is not a BaseModality")
         return m
 
+    def _host_stager(self, dev):
+        from .h2d import HostTensorStager
+        if getattr(self, "_stager", None) is None or self._stager.device != torch.device(dev):
+            self._stager = HostTensorStager(dev)
+        return self._stager
+
     def status(self) -> torch.Tensor:
         if self._status is None or self._status.device != self.embed_table.device:
             self._status = ops.new_status(self.embed_table.device)
@@ -98,7 +104,7 @@ class B200MultiModalEmbedder(torch.nn.Module):
                                       "gradient (freeze the LLM, or run under torch.no_grad())")
         if eager_checks and not input_ids.is_cuda:
             self._eager_host_checks(input_ids, stacks, positions_from)
-        ids = input_ids.to(dev, non_blocking=True)
+        ids = self._host_stager(dev).upload(input_ids)      # pageable host ids -> pinned staging -> async H2D
         st = self.status()
         B, S = ids.shape
         H = self.embed_table.shape[1]
@@ -116,8 +122,8 @@ class B200MultiModalEmbedder(torch.nn.Module):
                     dest_rows, _, _ = ops.attach_positions(ids, self.attachment_token_idx, expected_rows=n_rows,
                                                            want_src_of_pos=False, status=st)
                 else:
-                    bi = processed_multimodal_inputs["batch_idx"][name].to(dev, non_blocking=True)
-                    tr = processed_multimodal_inputs["token_range"][name].to(dev, non_blocking=True)
+                    bi = self._host_stager(dev).upload(processed_multimodal_inputs["batch_idx"][name])
+                    tr = self._host_stager(dev).upload(processed_multimodal_inputs["token_range"][name])
                     dest_rows = None
             fused = (self.fuse_splice and hasattr(modality, "forward_into") and embedded.dtype == torch.bfloat16
                      and not trains[name])

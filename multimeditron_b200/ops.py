@@ -297,6 +297,34 @@ def gemm_ln_bias_act(a: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None
     return out
 
 
+def gemm_grouped(a: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, groups: int, act: int = ACT_NONE,
+                 residual: torch.Tensor | None = None, out: torch.Tensor | None = None,
+                 out_row_map: torch.Tensor | None = None, stats_out: torch.Tensor | None = None,
+                 ln_stats: torch.Tensor | None = None, eps: float = 1e-5) -> torch.Tensor:
+    """`groups` same-shaped GEMMs in ONE launch (mm_gemm_grouped): a [groups*M, K], w [groups*N, K], bias [groups*N]
+    -> out [groups*M, N]; group g's rows multiply w[g*N:(g+1)*N].  M must be a multiple of 256."""
+    _cuda(a, w, bias, residual, out, out_row_map, stats_out, ln_stats)
+    lib = _lib.load()
+    assert a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and a.dim() == 2 and w.dim() == 2
+    assert a.stride(1) == 1 and w.stride(1) == 1
+    Mt, K = a.shape
+    assert Mt % groups == 0 and w.shape[0] % groups == 0 and w.shape[1] == K
+    M, N = Mt // groups, w.shape[0] // groups
+    if out is None:
+        assert out_row_map is None
+        out = torch.empty(Mt, N, dtype=torch.bfloat16, device=a.device)
+    assert out.dtype == torch.bfloat16 and out.stride(-1) == 1
+    ldc = out.stride(-2) if out.dim() >= 2 else N
+    ldr = residual.stride(-2) if residual is not None else 0
+    n_out_rows = (out.numel() // N if out.is_contiguous() else out.shape[0]) if out_row_map is not None else 0
+    with _timed("mm_gemm_bias_act", 2.0 * Mt * N * K):
+        rc = lib.mm_gemm_grouped(_ptr(a), a.stride(0), _ptr(w), w.stride(0), _ptr(bias), _ptr(out), ldc, M, N, K,
+                                 int(groups), int(act), _ptr(residual), ldr, _ptr(out_row_map), n_out_rows,
+                                 _ptr(stats_out), _ptr(ln_stats), float(eps), _stream())
+    _check(rc, "mm_gemm_grouped")
+    return out
+
+
 GEMM_FLAG_1CTA = 0x100   # per-call: OR into `act` to run the 1-CTA kernel instead of the CTA pair (bit-identical results)
 
 

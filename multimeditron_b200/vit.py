@@ -229,3 +229,80 @@ class TowerRunner:
         B = pixels.shape[0]
         y = self.project(self.features(pixels))
         return y.view(B, self.cfg.num_patches, -1)
+
+
+class GroupedTowerRunner:
+    """E same-shaped towers (the MoE modalities' experts, image_modality_moe.py:160-162) on STACKED activations: every
+    encoder GEMM of a layer is ONE `mm_gemm_grouped` launch for all experts (rows stacked expert-major, weights stacked
+    along their rows), attention ONE launch over E*B images.  5 experts x 150 tiles of a D x D GEMM fill 10.1 waves of
+    CTA pairs instead of 5 x 2.03 (the third wave of every per-expert launch was 3 % full).  Needs B*T % 256 == 0 (no row
+    tile may straddle two experts); `eligible()` says so and the caller keeps the per-expert path otherwise.  Results are
+    bit-identical to the per-expert runners (same kernels, same operands, same k order)."""
+
+    def __init__(self, weights: list):
+        assert len(weights) > 1 and all(w.cfg == weights[0].cfg for w in weights) and FOLD_LN
+        self.ws_list, self.cfg, self.E = weights, weights[0].cfg, len(weights)
+        self.device = weights[0].device
+        cat = lambda key, i: torch.cat([w.layers[i][key] for w in weights], 0).contiguous()  # noqa: E731
+        self.layers = []
+        for i in range(self.cfg.num_hidden_layers):
+            L = {k: cat(k, i) for k in ("wo", "bo", "w2", "b2", "w1_f", "b1_f")}
+            for k in (("wqkv_f", "bqkv_f") if i > 0 else ("wqkv", "bqkv")):
+                L[k] = cat(k, i)
+            self.layers.append(L)
+        self._ws = {}
+
+    def eligible(self, B: int) -> bool:
+        return (B * self.cfg.num_tokens) % 256 == 0 and self.cfg.has_cls
+
+    def _workspace(self, B: int):
+        key = (B, torch.cuda.current_stream(self.device).cuda_stream)
+        ws = self._ws.get(key)
+        if ws is None:
+            c, dev, E = self.cfg, self.device, self.E
+            M, D, I = E * B * c.num_tokens, c.hidden_size, c.intermediate_size
+            e = lambda *s: torch.empty(*s, dtype=torch.bfloat16, device=dev)  # noqa: E731
+            ws = dict(stats=torch.zeros(M, ops.row_stats_slots(D), 2, dtype=torch.float32, device=dev), x=e(M, D), h=e(M, D),
+                      qkv=e(M, 3 * c.num_attention_heads * self.ws_list[0].head_stride), attn=e(M, D), mlp=e(M, I))
+            m = torch.arange(M, device=dev, dtype=torch.int64)
+            t = m % c.num_tokens
+            ws["drop_cls"] = torch.where(t == 0, torch.full_like(m, -1),
+                                         (m // c.num_tokens) * c.num_patches + t - 1).to(torch.int32)
+            for k in [k for k in self._ws if k[1] == key[1]]:
+                del self._ws[k]
+            self._ws[key] = ws
+        return ws
+
+    def features(self, pixels: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+        """pixels [B,3,img,img] -> out [E, B*P, D] bf16 (every expert's CLS-dropped features, expert-major)."""
+        c, E = self.cfg, self.E
+        B = pixels.shape[0]
+        if pixels.shape[-1] != c.image_size or pixels.shape[-2] != c.image_size:
+            raise ValueError(f"Input image size ({pixels.shape[-2]}*{pixels.shape[-1]}) doesn't match model "
+                             f"({c.image_size}*{c.image_size}).")
+        assert self.eligible(B) and out.is_contiguous() and out.numel() == E * B * c.num_patches * c.hidden_size
+        ws = self._workspace(B)
+        x, h, qkv, attn, mlp, stats = ws["x"], ws["h"], ws["qkv"], ws["attn"], ws["mlp"], ws["stats"]
+        T, D, nh, hd, eps = c.num_tokens, c.hidden_size, c.num_attention_heads, c.head_dim, c.layer_norm_eps
+        Mg = B * T
+        act = ops.ACT_BY_NAME[c.hidden_act]
+        px = pixels.contiguous()
+        for e, w in enumerate(self.ws_list):       # patch embed + pre-LN + layer-0 LN1: per-expert parameters on row slices
+            xe = x[e * Mg:(e + 1) * Mg]
+            ops.patch_embed(px, w.patch_w, w.patch_b, w.pos, w.cls, c.patch_size, out=xe.view(B, T, D))
+            ops.layernorm(xe, w.pre_ln[0], w.pre_ln[1], eps, out=xe)
+            ops.layernorm(xe, w.layers[0]["ln1"][0], w.layers[0]["ln1"][1], eps, out=h[e * Mg:(e + 1) * Mg])
+        n_layers = len(self.layers)
+        for i, L in enumerate(self.layers):
+            if i == 0:
+                ops.gemm_grouped(h, L["wqkv"], L["bqkv"], E, out=qkv)
+            else:
+                ops.gemm_grouped(x, L["wqkv_f"], L["bqkv_f"], E, out=qkv, ln_stats=stats, eps=eps)
+            ops.attention_fwd(qkv, E * B, T, nh, hd, hd ** -0.5, out=attn)
+            ops.gemm_grouped(attn, L["wo"], L["bo"], E, residual=x, out=x, stats_out=stats)
+            ops.gemm_grouped(x, L["w1_f"], L["b1_f"], E, act=act, out=mlp, ln_stats=stats, eps=eps)
+            if i < n_layers - 1:
+                ops.gemm_grouped(mlp, L["w2"], L["b2"], E, residual=x, out=x, stats_out=stats)
+            else:   # last fc2 writes the compact [E*B*P, D] feature matrix directly (CLS rows never stored)
+                ops.gemm_grouped(mlp, L["w2"], L["b2"], E, residual=x, out=out.view(-1, D), out_row_map=ws["drop_cls"])
+        return out

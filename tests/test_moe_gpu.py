@@ -173,3 +173,61 @@ def test_conv_rows_and_pools_bit_exact():
     lin = ops.gemm_bias_act(a, w, b)
     assert torch.equal(got, torch.relu((lin.float() + r.float()).bfloat16()))
     assert torch.equal(ops.gemm_bias_act(a, w, b, act=ops.ACT_RELU), torch.relu(lin))
+
+
+def test_grouped_gemm_bit_identical_to_per_group_launches():
+    """mm_gemm_grouped: G same-shaped GEMMs in one launch == G launches (plain, residual + stats producer, LN-fold consumer,
+    row-mapped output), bit for bit; a row count that would let a tile straddle two groups is refused."""
+    from multimeditron_b200 import ops
+    G, M, N, K = 3, 512, 768, 256
+    g0 = torch.Generator().manual_seed(9)
+    a = torch.randn(G * M, K, generator=g0).bfloat16().to(DEV)
+    w = (torch.randn(G * N, K, generator=g0) * 0.05).bfloat16().to(DEV)
+    b = torch.randn(G * N, generator=g0).bfloat16().to(DEV)
+    res = torch.randn(G * M, N, generator=g0).bfloat16().to(DEV)
+    per = lambda fn: torch.cat([fn(g) for g in range(G)], 0)  # noqa: E731
+    sl = lambda t, g, n: t[g * n:(g + 1) * n]                   # noqa: E731
+    assert torch.equal(ops.gemm_grouped(a, w, b, G, act=1),
+                       per(lambda g: ops.gemm_bias_act(sl(a, g, M), sl(w, g, N), sl(b, g, N), act=1)))
+    st = torch.zeros(G * M, ops.row_stats_slots(N), 2, device=DEV)
+    got = ops.gemm_grouped(a, w, b, G, residual=res, stats_out=st)
+    st1 = torch.zeros_like(st)
+    want = per(lambda g: ops.gemm_ln_bias_act(sl(a, g, M), sl(w, g, N), sl(b, g, N), residual=sl(res, g, M),
+                                              stats_out=sl(st1, g, M)))
+    assert torch.equal(got, want) and torch.equal(st, st1)
+    lns = (torch.rand(G * M, ops.row_stats_slots(K), 2, generator=g0) * 64 + 0.5).to(DEV)
+    assert torch.equal(ops.gemm_grouped(a, w, b, G, act=1, ln_stats=lns, eps=1e-5),
+                       per(lambda g: ops.gemm_ln_bias_act(sl(a, g, M), sl(w, g, N), sl(b, g, N), act=1,
+                                                          ln_stats=sl(lns, g, M), eps=1e-5)))
+    rmap = torch.randperm(G * M, generator=g0).int().to(DEV)
+    rmap[::7] = -1
+    o1 = torch.full((G * M, N), 3.0, device=DEV).bfloat16()
+    o2 = o1.clone()
+    ops.gemm_grouped(a, w, b, G, out=o1, out_row_map=rmap)
+    for g in range(G):
+        ops.gemm_bias_act(sl(a, g, M), sl(w, g, N), sl(b, g, N), out=o2, out_row_map=sl(rmap, g, M))
+    assert torch.equal(o1, o2)
+    with pytest.raises(ops.MMError):
+        ops.gemm_grouped(a[:G * 384].contiguous(), w, b, G)    # 384 rows per group: a 256-row tile would straddle groups
+
+
+def test_grouped_experts_equal_per_expert_runners(monkeypatch):
+    """vit.GroupedTowerRunner (one grouped launch per layer op for all experts) against the per-expert runners."""
+    cfg = TOWERS["tiny"]        # T = 17: B*T % 256 == 0 needs B = 256
+    E, hidden, B = 3, 64, 256
+    names = [f"expert{i}" for i in range(E)]
+    mcfg = AutoModality.config_from_dict({
+        "model_type": "moe_meditron_clip_b200", "hidden_size": hidden, "expert_clip_names": names,
+        "expert_towers": {n: "tiny" for n in names}, "image_processor": "tiny", "fusion_method": "weighted_average",
+        "top_k_experts": 1, "gating_class_names": [names[i] for i in (2, 0, 1)]})
+    sd = synth.make_moe_state_dict([cfg] * E, hidden, False, seed=4)
+    w = torch.softmax(torch.randn(B, E, generator=torch.Generator().manual_seed(2)), -1)
+    px = synth.make_pixels(cfg, B, seed=3).to(DEV)
+    m = AutoModality.from_config(mcfg).load_reference_state_dict(sd, DEV, gating=lambda p: w.to(p.device))
+    assert m._grouped is not None and m._grouped.eligible(B)
+    y = m(px)
+    monkeypatch.setenv("MM_B200_MOE_GROUPED", "0")
+    m2 = AutoModality.from_config(mcfg).load_reference_state_dict(sd, DEV, gating=lambda p: w.to(p.device))
+    assert m2._grouped is None
+    assert torch.equal(y, m2(px))
+    assert not m._grouped.eligible(3) and torch.equal(m(px[:3]), m2(px[:3]))     # ineligible batch: per-expert path

@@ -62,3 +62,24 @@ def test_kernel_flags_an_image_block_that_runs_past_the_row():
     st = ops.new_status("cuda")
     ops.position_ids(torch.ones(1, 10, dtype=torch.int64).cuda(), ids.cuda(), 3, 4, 2, use_2d=True, status=st)
     assert int(st.item()) & ops.STATUS_COUNT_MISMATCH
+
+
+@pytest.mark.gpu
+def test_adjacent_images_without_delimiters_are_two_images():
+    """The k-th image starts at the (k*P)-th attachment token of the row (compute_token_range, prompt_tokenizers.py:255-286),
+    not at the start of a run of attachment ids: two images that touch are still two images."""
+    grid, V = 3, 100
+    P, att = grid * grid, V - 2
+    ids = torch.randint(0, V - 4, (2, 40))
+    ids[0, 5:5 + 2 * P] = att                 # two images back to back
+    ids[1, 0:P] = att                         # one at the row start ...
+    ids[1, P:2 * P] = att                     # ... immediately followed by another
+    ids[1, 30:30 + P] = att
+    mask = torch.ones(2, 40, dtype=torch.bool)
+    ranges = [splice_oracle.compute_token_range(ids[0].numpy(), [P, P], att),
+              splice_oracle.compute_token_range(ids[1].numpy(), [P, P, P], att)]
+    assert ranges[0] == [(5, 5 + P), (5 + P, 5 + 2 * P)]
+    want = splice_oracle.position_ids(mask.numpy(), ranges, grid, True)
+    st = ops.new_status("cuda")
+    got = ops.position_ids(mask.cuda(), ids.cuda(), att, P, grid, use_2d=True, status=st)
+    assert np.array_equal(got.cpu().numpy(), want) and int(st.item()) == 0
