@@ -90,11 +90,6 @@ struct Cfg {
 #define MM_ATTN3_ISSUER_SLEEP 0
 #endif
 // MM_ATTN3_PACKED: scale-and-shift and row-sum adds as fp32x2 instructions (FFMA2 / FADD2)
-// MM_ATTN3_LATE_PFULL: P(k) is published to the MMA issuer (wait::st + arrive) only after the TMEM load of S(k+1) has
-// been issued, so the store's and the load's TMEM round trips overlap instead of following each other.
-#ifndef MM_ATTN3_LATE_PFULL
-#define MM_ATTN3_LATE_PFULL 0
-#endif
 #ifndef MM_ATTN3_PACKED
 #define MM_ATTN3_PACKED 1
 #endif
@@ -384,8 +379,6 @@ __global__ void __launch_bounds__(Cfg<BKV, NSTR>::kThreads, 1)
         const int qt = sc.first_qt(s, g) + NSTR * j;
         const bool warp_live = qt * kBQ + q * 32 < p.T;  // warps whose 32 rows are all padding only keep the protocol
         float m_run = -INFINITY, l_run = 0.f;            // running max (raw score units) and row sum
-        bool p_pending = false;
-        (void)p_pending;
         for (int kt = 0; kt < nkv; ++kt, ++it) {
           const int valid = p.T - kt * BKV;  // columns >= valid are padding (only in the last kv tile)
           mbar_wait(&bars->s_full[s], it & 1);
@@ -396,17 +389,8 @@ __global__ void __launch_bounds__(Cfg<BKV, NSTR>::kThreads, 1)
 #pragma unroll
             for (int c = 0; c < NCH; ++c)
               if (c * 32 < valid) tmem_ld_32x32b_x32(t_S + c * 32, sv + c * 32);
+            tc_wait_ld();
           }
-#if MM_ATTN3_LATE_PFULL
-          if (p_pending) {   // publish P of the previous step while S of this one streams into the registers
-            if (warp_live) tc_wait_st();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&bars->p_full[s]);
-            p_pending = false;
-          }
-#endif
-          if (warp_live) tc_wait_ld();
           TR_SM(1);
           // the S accumulator now lives in registers: hand it back for the next QK^T right away
           tc_fence_before();
@@ -524,28 +508,13 @@ __global__ void __launch_bounds__(Cfg<BKV, NSTR>::kThreads, 1)
             m_run = m_new;
 #pragma unroll
             for (int c = 0; c < BKV / 64; ++c) tmem_st_32x32b_x32(t_P + c * 32, pk + c * 32);
-#if !MM_ATTN3_LATE_PFULL
             tc_wait_st();
-#endif
           }
           TR_SM(4);
-#if MM_ATTN3_LATE_PFULL
-          p_pending = true;
-#else
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&bars->p_full[s]);
-#endif
         }
-#if MM_ATTN3_LATE_PFULL
-        if (p_pending) {
-          if (warp_live) tc_wait_st();
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&bars->p_full[s]);
-          p_pending = false;
-        }
-#endif
         // ---- epilogue of the q tile: O / l -> bf16 -> global ----
         mbar_wait(&bars->pv_done[s], (it - 1) & 1);
         tc_fence_after();

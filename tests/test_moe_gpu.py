@@ -223,11 +223,12 @@ def test_grouped_experts_equal_per_expert_runners(monkeypatch):
     sd = synth.make_moe_state_dict([cfg] * E, hidden, False, seed=4)
     w = torch.softmax(torch.randn(B, E, generator=torch.Generator().manual_seed(2)), -1)
     px = synth.make_pixels(cfg, B, seed=3).to(DEV)
-    m = AutoModality.from_config(mcfg).load_reference_state_dict(sd, DEV, gating=lambda p: w.to(p.device))
+    gate = lambda p: w[:p.shape[0]].to(p.device)     # noqa: E731
+    m = AutoModality.from_config(mcfg).load_reference_state_dict(sd, DEV, gating=gate)
     assert m._grouped is not None and m._grouped.eligible(B)
     y = m(px)
     monkeypatch.setenv("MM_B200_MOE_GROUPED", "0")
-    m2 = AutoModality.from_config(mcfg).load_reference_state_dict(sd, DEV, gating=lambda p: w.to(p.device))
+    m2 = AutoModality.from_config(mcfg).load_reference_state_dict(sd, DEV, gating=gate)
     assert m2._grouped is None
     assert torch.equal(y, m2(px))
     assert not m._grouped.eligible(3) and torch.equal(m(px[:3]), m2(px[:3]))     # ineligible batch: per-expert path
