@@ -90,6 +90,10 @@ struct Cfg {
 #define MM_ATTN3_ISSUER_SLEEP 0
 #endif
 // MM_ATTN3_PACKED: scale-and-shift and row-sum adds as fp32x2 instructions (FFMA2 / FADD2)
+// MM_ATTN3_INDEP: T <= 128 -> every stream works on its own (image, head) unit (see Sched)
+#ifndef MM_ATTN3_INDEP
+#define MM_ATTN3_INDEP 1
+#endif
 #ifndef MM_ATTN3_PACKED
 #define MM_ATTN3_PACKED 1
 #endif
@@ -149,15 +153,24 @@ __device__ __forceinline__ bool bar_test(uint64_t* bar, uint32_t parity) {
 // Work decomposition shared by every role.  The CTA owns units u_i = blockIdx.x + i*gridDim.x.  A K/V "group" is
 // what travels through the ring together: the whole unit when it fits (resident), else one query NSTR-tuple of it.
 // Stream s owns, in group g, the query tiles first_qt(s,g) + NSTR*j, j < ntiles(s,g).
+// T <= 128 (one query tile per unit: CLIP ViT-B/32, T = 50): the streams would share nothing but idle time, so each
+// stream takes its OWN unit ("indep": group g = units NSTR*g .. NSTR*g + NSTR-1 of this CTA, stream s owns unit
+// NSTR*g + s and its private K/V slots) — three units in flight per SM instead of one.
 template <int NSTR>
 struct Sched {
   int nkv, nq, ntup, n_units, ngroups;
-  bool resident;
+  bool resident, indep;
   __device__ __forceinline__ int unit_ord(int g) const { return resident ? g : g / ntup; }
+  // ordinal (in this CTA's unit list) of the unit stream s works on in group g
+  __device__ __forceinline__ int unit_of(int s, int g) const { return indep ? NSTR * g + s : unit_ord(g); }
+  // ring sequence number of K/V tile kt of the unit stream s works on in group g
+  __device__ __forceinline__ int kv_seq(int s, int g, int kt) const { return (indep ? NSTR * g + s : g) * nkv + kt; }
   __device__ __forceinline__ int first_qt(int s, int g) const {
+    if (indep) return 0;
     return resident ? s : NSTR * (g - unit_ord(g) * ntup) + s;
   }
   __device__ __forceinline__ int ntiles(int s, int g) const {
+    if (indep) return NSTR * g + s < n_units ? 1 : 0;
     const int f = first_qt(s, g);
     if (f >= nq) return 0;
     return resident ? (nq - f + NSTR - 1) / NSTR : 1;
@@ -183,8 +196,10 @@ __global__ void __launch_bounds__(Cfg<BKV, NSTR>::kThreads, 1)
   sc.nq = (p.T + kBQ - 1) / kBQ;
   sc.ntup = (sc.nq + NSTR - 1) / NSTR;
   sc.resident = sc.nkv <= NS;  // whole unit fits in the ring: load K/V once per unit
+  sc.indep = MM_ATTN3_INDEP && sc.nq == 1 && NSTR * sc.nkv <= NS;
   sc.n_units = ((int)blockIdx.x < units) ? (units - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
-  sc.ngroups = sc.n_units * (sc.resident ? 1 : sc.ntup);
+  sc.ngroups = sc.indep ? (sc.n_units + NSTR - 1) / NSTR : sc.n_units * (sc.resident ? 1 : sc.ntup);
+  const int kv_items = sc.indep ? sc.n_units : sc.ngroups;   // what the K/V producer walks: units (indep) or groups
   const int nkv = sc.nkv;
 
   if (warp == 1 && lane == 0) {
@@ -192,7 +207,8 @@ __global__ void __launch_bounds__(Cfg<BKV, NSTR>::kThreads, 1)
     tma_prefetch_desc(&maps.kv);
     for (int i = 0; i < NS; ++i) {
       mbar_init(&bars->kv_full[i], 1);
-      mbar_init(&bars->kv_empty[i], NSTR);  // one release per stream (real tile: tcgen05.commit; none: plain arrive)
+      // one release per stream that sees the slot (real tile: tcgen05.commit; none: plain arrive); private slots: one
+      mbar_init(&bars->kv_empty[i], sc.indep ? 1 : NSTR);
     }
     for (int s = 0; s < NSTR; ++s) {
       mbar_init(&bars->q_full[s], 1);
@@ -230,14 +246,14 @@ __global__ void __launch_bounds__(Cfg<BKV, NSTR>::kThreads, 1)
           while (q_g[s] < sc.ngroups && sc.ntiles(s, q_g[s]) == 0) ++q_g[s];
         }
         for (;;) {
-          bool pending = kv_g < sc.ngroups;
+          bool pending = kv_g < kv_items;
 #pragma unroll
           for (int s = 0; s < NSTR; ++s) pending |= q_g[s] < sc.ngroups;
           if (!pending) break;
           bool progress = false;
-          if (kv_g < sc.ngroups && bar_test(&bars->kv_empty[kv_stage], kv_phase ^ 1)) {
+          if (kv_g < kv_items && bar_test(&bars->kv_empty[kv_stage], kv_phase ^ 1)) {
             progress = true;
-            const int u = blockIdx.x + sc.unit_ord(kv_g) * gridDim.x;
+            const int u = blockIdx.x + (sc.indep ? kv_g : sc.unit_ord(kv_g)) * gridDim.x;
             const int b = u / p.heads, h = u - b * p.heads;
             uint64_t* full = &bars->kv_full[kv_stage];
             uint8_t* st = sKV + kv_stage * C::kStageBytes;
@@ -252,7 +268,7 @@ __global__ void __launch_bounds__(Cfg<BKV, NSTR>::kThreads, 1)
             if (q_g[s] < sc.ngroups && bar_test(&bars->q_empty[s], (q_n[s] & 1) ^ 1)) {
               progress = true;
               const int g = q_g[s];
-              const int u = blockIdx.x + sc.unit_ord(g) * gridDim.x;
+              const int u = blockIdx.x + sc.unit_of(s, g) * gridDim.x;
               const int b = u / p.heads, h = u - b * p.heads;
               const int qt = sc.first_qt(s, g) + NSTR * q_j[s];
               mbar_arrive_expect_tx(&bars->q_full[s], C::kQTile);
@@ -279,7 +295,7 @@ __global__ void __launch_bounds__(Cfg<BKV, NSTR>::kThreads, 1)
         TR_DECL
         int cnt = sc.ngroups ? sc.ntiles(s, 0) : 0;
         auto slot_of = [&](int g, int kt, int& stage, uint32_t& phase) {
-          const int seq = g * nkv + kt;
+          const int seq = sc.kv_seq(s, g, kt);
           const int r = seq / NS;
           stage = seq - r * NS;
           phase = (uint32_t)r & 1u;
@@ -291,6 +307,10 @@ __global__ void __launch_bounds__(Cfg<BKV, NSTR>::kThreads, 1)
         while (cg < sc.ngroups) {
           int stage;
           uint32_t phase;
+          if (cnt == 0 && sc.indep) {   // private slots: nothing to hand back
+            if (++cg < sc.ngroups) cnt = sc.ntiles(s, cg);
+            continue;
+          }
           if (cnt == 0) {
             // this stream has no query tile in the group: only hand its share of the K/V slots back
             slot_of(cg, kp, stage, phase);
@@ -372,7 +392,7 @@ __global__ void __launch_bounds__(Cfg<BKV, NSTR>::kThreads, 1)
     uint32_t it = 0;
     TR_DECL
     for (int g = 0; g < sc.ngroups; ++g) {
-      const int u = blockIdx.x + sc.unit_ord(g) * gridDim.x;
+      const int u = blockIdx.x + sc.unit_of(s, g) * gridDim.x;
       const int b = u / p.heads, h = u - b * p.heads;
       const int nt = sc.ntiles(s, g);
       for (int j = 0; j < nt; ++j) {
