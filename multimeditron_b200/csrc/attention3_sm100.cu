@@ -90,6 +90,14 @@ struct Cfg {
 #define MM_ATTN3_ISSUER_SLEEP 0
 #endif
 // MM_ATTN3_PACKED: scale-and-shift and row-sum adds as fp32x2 instructions (FFMA2 / FADD2)
+// MM_ATTN3_POLY: share of the exponentials computed on the FMA pipe instead of the MUFU pipe (FlashAttention-4's trick):
+// 2^x = 2^round(x) * p(x - round(x)), round by the magic-number add, p = degree-3 minimax polynomial of 2^f on
+// [-0.5, 0.5] (relative error 7.7e-5, far below the bf16 rounding of P), the power of two added into the exponent field.
+// 0 = none, 1 = two of every eight scores (25 %), 2 = two of every four (50 %).  The exp phase of the three lock-stepped
+// softmax warps is MUFU-pipe bound (8.7 clk per ex2) while the FMA pipe idles at 18 %.
+#ifndef MM_ATTN3_POLY
+#define MM_ATTN3_POLY 0
+#endif
 // MM_ATTN3_INDEP: T <= 128 -> every stream works on its own (image, head) unit (see Sched)
 #ifndef MM_ATTN3_INDEP
 #define MM_ATTN3_INDEP 1
@@ -126,6 +134,25 @@ __device__ __forceinline__ float ex2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// two exponentials on the FMA pipe (packed fp32x2): x in [-126, ~16]
+__device__ __forceinline__ void ex2_poly2(uint64_t xv, float& pa, float& pb) {
+  float xa, xb;
+  f32x2_unpack(xv, xa, xb);
+  xa = fmaxf(xa, -126.f), xb = fmaxf(xb, -126.f);                       // masked (-inf) and far-below-max scores
+  const uint64_t x = f32x2(xa, xb);
+  const uint64_t xr = add_f32x2(x, f32x2(12582912.f, 12582912.f));      // 1.5 * 2^23: round(x) lands in the low mantissa bits
+  const uint64_t n = add_f32x2(xr, f32x2(-12582912.f, -12582912.f));
+  const uint64_t f = fma_f32x2(n, f32x2(-1.f, -1.f), x);                // x - round(x) in [-0.5, 0.5]
+  uint64_t pl = fma_f32x2(f, f32x2(0.05508868396282196f, 0.05508868396282196f), f32x2(0.24260404706001282f, 0.24260404706001282f));
+  pl = fma_f32x2(pl, f, f32x2(0.6932762265205383f, 0.6932762265205383f));
+  pl = fma_f32x2(pl, f, f32x2(0.9999289512634277f, 0.9999289512634277f));
+  float ra, rb, qa, qb;
+  f32x2_unpack(xr, ra, rb);
+  f32x2_unpack(pl, qa, qb);
+  pa = __int_as_float(__float_as_int(qa) + (__float_as_int(ra) << 23));
+  pb = __int_as_float(__float_as_int(qb) + (__float_as_int(rb) << 23));
+}
+
 __device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
   asm volatile(
       "{\n\t"
@@ -444,8 +471,15 @@ __global__ void __launch_bounds__(Cfg<BKV, NSTR>::kThreads, 1)
   do {                                                                                                            \
     float x0, x1, x2, x3;                                                                                         \
     f32x2_unpack(fma_f32x2(f32x2(__uint_as_float(sv[(jj) + 0]), __uint_as_float(sv[(jj) + 1])), k2, nm2), x0, x1); \
-    f32x2_unpack(fma_f32x2(f32x2(__uint_as_float(sv[(jj) + 2]), __uint_as_float(sv[(jj) + 3])), k2, nm2), x2, x3); \
-    const float p0 = ex2(x0), p1 = ex2(x1), p2 = ex2(x2), p3 = ex2(x3);                                           \
+    const uint64_t xq = fma_f32x2(f32x2(__uint_as_float(sv[(jj) + 2]), __uint_as_float(sv[(jj) + 3])), k2, nm2);    \
+    float p2, p3;                                                                                                 \
+    if (MM_ATTN3_POLY == 2 || (MM_ATTN3_POLY == 1 && (((jj) >> 2) & 1))) {                                         \
+      ex2_poly2(xq, p2, p3);                                                                                      \
+    } else {                                                                                                      \
+      f32x2_unpack(xq, x2, x3);                                                                                   \
+      p2 = ex2(x2), p3 = ex2(x3);                                                                                 \
+    }                                                                                                             \
+    const float p0 = ex2(x0), p1 = ex2(x1);                                                                       \
     sa = add_f32x2(sa, f32x2(p0, p1));                                                                            \
     sb = add_f32x2(sb, f32x2(p2, p3));                                                                            \
     pk[(jj) >> 1] = pack_bf16x2(p0, p1);                                                                          \
