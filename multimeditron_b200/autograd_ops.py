@@ -109,3 +109,30 @@ class SpliceRowsFunction(torch.autograd.Function):
 def splice_rows(dest2d: torch.Tensor, src: torch.Tensor, rows: torch.Tensor, status=None) -> torch.Tensor:
     """dest2d[rows[k]] = src[k] in place, differentiable w.r.t. src (model.py:441-444)."""
     return SpliceRowsFunction.apply(dest2d, src, rows.to(torch.int32).contiguous(), status)
+
+
+class WeightedExpertSumFunction(torch.autograd.Function):
+    """fused[b,p,:] = sum_e w[b, perm[e]] * x[e,b,p,:]  (image_modality_moe.py:171-177, image_modality_moe_pep.py:212-216)
+    with a backward for x (the per-expert projector outputs of the PEP variant, whose projectors train in the ALIGNMENT
+    stage): dx[e] = w[:, perm[e]] * dfused.  The gate is frozen there (freeze_modality_embedder), so w gets no gradient."""
+
+    @staticmethod
+    def forward(ctx, x, w, perm, B, P):
+        ctx.save_for_backward(w, perm if perm is not None else torch.empty(0))
+        ctx.meta = (B, P, perm is not None, x.shape[0])
+        return ops.weighted_expert_sum(x.detach().contiguous(), w, perm, B, P)
+
+    @staticmethod
+    def backward(ctx, g):
+        w, perm = ctx.saved_tensors
+        B, P, has_perm, E = ctx.meta
+        gb = g.detach().to(torch.bfloat16).contiguous()[None]          # [1, B*P, D]
+        outs = []
+        for e in range(E):
+            col = int(perm[e]) if has_perm else e
+            outs.append(ops.weighted_expert_sum(gb, w[:, col:col + 1].contiguous(), None, B, P))   # bf16(w * g), like autograd
+        return torch.stack(outs, 0), None, None, None, None
+
+
+def weighted_expert_sum(x, w, perm, B, P):
+    return WeightedExpertSumFunction.apply(x, w, perm, B, P)

@@ -240,9 +240,21 @@ class _B200MOEBase(BaseModality):
         return m
 
     # -- the plugin call ------------------------------------------------------------------------------------------
-    @torch.no_grad()
+    @property
+    def projector_trainable(self) -> bool:
+        mods = [m for m in (getattr(self, "projector", None), getattr(self, "projectors", None)) if m is not None]
+        return any(p.requires_grad for m in mods for p in m.parameters())
+
     def forward(self, inputs) -> torch.Tensor:
-        """-> [B, P, H] (weighted_average) or [B, E*P, H] (sequence_append), bf16."""
+        """-> [B, P, H] (weighted_average / cross_attn) or [B, E*P, H] (sequence_append), bf16.
+        ALIGNMENT stage (`unfreeze_projection()`, autograd on): experts, gate and fusion run on the kernels without a
+        graph, the projector(s) as `autograd_ops.ProjectorFunction` (forward + backward)."""
+        if torch.is_grad_enabled() and self.projector_trainable:
+            return self._forward_train(inputs)
+        with torch.no_grad():
+            return self._forward_infer(inputs)
+
+    def _forward_infer(self, inputs) -> torch.Tensor:
         px = self._stack(inputs)
         B, E, P, H = px.shape[0], len(self.towers), self._num_patches_per_entry, self.config.hidden_size
         n_out = E * P if self.fusion_method == "sequence_append" else P
@@ -350,15 +362,41 @@ class _B200MOEBase(BaseModality):
     def _run(self, px: torch.Tensor, out2d: torch.Tensor, dest_rows: Optional[torch.Tensor]):
         raise NotImplementedError
 
-    # -- training-mode switches (interface parity; backward is not part of this round) ------------------------------
+    def _forward_train(self, inputs) -> torch.Tensor:
+        raise NotImplementedError
+
+    # -- training-mode switches (image_modality_moe.py:222-246, image_modality_moe_pep.py:263-288) ------------------
     def freeze_modality_embedder(self):
         self.modality_frozen = True
 
     def unfreeze_modality_embedder(self):
-        raise NotImplementedError("ViT/gating backward on the B200 path is SURVEY.md §8(f)#2 (next)")
+        raise NotImplementedError("ViT / gating backward is not part of the B200 path (SURVEY.md §8(f)#2 lists it as "
+                                  "optional); the ALIGNMENT stage (projectors only) is: unfreeze_projection()")
 
     def unfreeze_projection(self):
-        raise NotImplementedError("projector backward on the B200 path is SURVEY.md §8(f)#2 (next)")
+        """model.py:310-326 (freeze_for_alignment): expose the projector(s) as nn.Parameters that SHARE storage with the
+        kernel-side weights (`projector.projection.*` for the shared variant, `projectors.<e>.projection.*` for PEP — the
+        reference's state-dict keys), so an optimizer's in-place updates are what the next forward multiplies by."""
+        from .image_modality import _ProjectorParams
+        if self.fusion_method == "cross_attn":
+            raise NotImplementedError("cross_attn fusion keeps its CrossAttention parameters trainable in the reference's "
+                                      "ALIGNMENT stage (they are never frozen): its backward is not built")
+        if self.per_expert_projector:
+            if getattr(self, "projectors", None) is None:
+                self.projectors = torch.nn.ModuleList([_ProjectorParams(pw) for pw in self._projs])
+            mods = self.projectors
+        else:
+            if getattr(self, "projector", None) is None:
+                self.projector = _ProjectorParams(self._projs[0])
+            mods = self.projector
+        for p in mods.parameters():
+            p.requires_grad = True
+
+    def freeze_projection(self):
+        for m in (getattr(self, "projector", None), getattr(self, "projectors", None)):
+            if m is not None:
+                for p in m.parameters():
+                    p.requires_grad = False
 
 
 @AutoModality.register("moe_meditron_clip_b200")
@@ -386,6 +424,26 @@ class B200MOEImageModality(_B200MOEBase):
             self._each_expert(lambda e, r: r.features(px, out=fused, out_row_map=maps[e]))
             self._join_experts()
         r0.project(fused, proj, out=out2d, out_row_map=dest_rows)                  # :207
+
+
+    def _forward_train(self, inputs) -> torch.Tensor:
+        """Shared projector after the fusion: everything before it runs without a graph."""
+        from ..autograd_ops import projector_forward
+        with torch.no_grad():
+            px = self._stack(inputs)
+            B, E, P = px.shape[0], len(self.towers), self._num_patches_per_entry
+            D = self._native_embed_dim
+            if self.fusion_method == "weighted_average":
+                stack = torch.empty(E, B * P, D, dtype=torch.bfloat16, device=self._device)
+                w = self._experts_and_gate(px, stack)
+                fused = ops.weighted_expert_sum(stack, w, self._perm, B, P)
+            else:
+                fused = torch.empty(B * E * P, D, dtype=torch.bfloat16, device=self._device)
+                maps = [self._append_map(B, e) for e in range(E)]
+                self._each_expert(lambda e, r: r.features(px, out=fused, out_row_map=maps[e]))
+                self._join_experts()
+            self._release()
+        return projector_forward(fused, self.projector).view(B, -1, self.config.hidden_size)
 
 
 @AutoModality.register("moe_meditron_clip_pep_b200")
@@ -424,3 +482,23 @@ class B200MOEImageModalityPEP(_B200MOEBase):
                 maps.append(m if dest_rows is None else dest_rows[m.long()].contiguous())
             self._each_expert(lambda e, r: r.project(r.features(px), self._projs[e], out=out2d, out_row_map=maps[e]))
             self._join_experts()
+
+    def _forward_train(self, inputs) -> torch.Tensor:
+        """One trainable projector per expert, fusion AFTER them: features without a graph, projectors and the weighted sum
+        (or the concatenation) under autograd."""
+        from ..autograd_ops import projector_forward, weighted_expert_sum
+        with torch.no_grad():
+            px = self._stack(inputs)
+            B, E, P, H = px.shape[0], len(self.towers), self._num_patches_per_entry, self.config.hidden_size
+            feats = torch.empty(E, B * P, self._native_embed_dim, dtype=torch.bfloat16, device=self._device)
+            if self.fusion_method == "weighted_average":
+                w = self._experts_and_gate(px, feats)
+            else:
+                self._each_expert(lambda e, r: r.features(px, out=feats[e]))
+                self._join_experts()
+            self._release()
+        ys = [projector_forward(feats[e], self.projectors[e]) for e in range(E)]             # [B*P, H] each
+        if self.fusion_method == "weighted_average":
+            return weighted_expert_sum(torch.stack(ys, 0), w, None, B, P).view(B, P, H)      # :212-216 (no permutation)
+        return torch.stack([y.view(B, P, H) for y in ys], 1).reshape(B, E * P, H)            # :206-209
+

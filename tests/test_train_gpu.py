@@ -180,3 +180,60 @@ def test_embedder_alignment_step_mirror_class():
     with torch.no_grad():
         after = emb(ids, pmi, positions_from="device")
     assert not torch.equal(after, base)                                    # the kernels multiply by the updated weights
+
+
+@pytest.mark.parametrize("pep,fusion", [(False, "weighted_average"), (False, "sequence_append"),
+                                        (True, "weighted_average"), (True, "sequence_append")])
+def test_moe_alignment_stage_projector_gradients(pep, fusion):
+    """ALIGNMENT stage of the MoE modalities (freeze_for_alignment -> unfreeze_projection + freeze_modality_embedder,
+    model.py:310-326; image_modality_moe.py:222-246, image_modality_moe_pep.py:263-288): experts / gate / fusion on the
+    kernels without a graph, the projector(s) under autograd.  Gradients of every projector tensor against torch
+    autograd through the oracle (fp32 ground truth, bf16 = the reference's own regime)."""
+    from multimeditron_b200.configs import TOWERS
+    from multimeditron_b200.modalities import AutoModality
+    cfg, E, hidden, B = TOWERS["tiny"], 3, 64, 5
+    names = [f"expert{i}" for i in range(E)]
+    perm = [2, 0, 1]
+    mcfg = AutoModality.config_from_dict({
+        "model_type": "moe_meditron_clip_pep_b200" if pep else "moe_meditron_clip_b200", "hidden_size": hidden,
+        "expert_clip_names": names, "expert_towers": {n: "tiny" for n in names}, "image_processor": "tiny",
+        "fusion_method": fusion, "top_k_experts": E if fusion == "sequence_append" else 1,
+        "gating_class_names": [names[i] for i in perm]})
+    sd = synth.make_moe_state_dict([cfg] * E, hidden, pep, seed=12)
+    w = torch.softmax(torch.randn(B, E, generator=torch.Generator().manual_seed(1)), -1)
+    px = synth.make_pixels(cfg, B, seed=2)
+    m = AutoModality.from_config(mcfg).load_reference_state_dict(sd, DEV, gating=lambda p: w.to(p.device))
+    m.unfreeze_projection()
+    m.freeze_modality_embedder()
+    assert m.projector_trainable
+    y = m([px[i] for i in range(B)])
+    assert y.requires_grad
+    dy = (torch.randn(y.shape, generator=torch.Generator().manual_seed(3)) * 0.1).to(DEV)
+    y.backward(dy.to(y.dtype))
+    pkeys = [k for k in sd if k.startswith("projector.") or k.startswith("projectors.")]
+    mods = m.projectors if pep else m.projector
+    got = {("projectors." if pep else "projector.") + n: p.grad.float() for n, p in mods.named_parameters()}
+    assert set(got) == set(pkeys), (sorted(got)[:3], sorted(pkeys)[:3])
+
+    def run(dtype):
+        p = {k: (v.detach().clone().to(DEV, dtype).requires_grad_(True) if k in pkeys else v.to(DEV, dtype))
+             for k, v in sd.items()}
+        out = vit_oracle.moe_modality_forward(p, [cfg] * E, px.to(DEV, dtype), w.to(DEV, dtype), perm, fusion, pep)
+        out.backward(dy.to(dtype))
+        return out.detach().float(), {k: p[k].grad.float() for k in pkeys}
+
+    y32, g32 = run(torch.float32)
+    ybf, gbf = run(torch.bfloat16)
+    _close(y.detach(), y32)
+    for k in pkeys:
+        scale = g32[k].abs().max().item()
+        err, ref_err = (got[k] - g32[k]).abs().max().item(), (gbf[k] - g32[k]).abs().max().item()
+        assert err <= 2.0 * ref_err + 2e-2 * scale, (k, err, ref_err, scale)
+    # one optimizer step moves the weights the NEXT forward multiplies by (shared storage)
+    opt = torch.optim.SGD(mods.parameters(), lr=0.5)
+    opt.step()
+    with torch.no_grad():
+        y2 = m([px[i] for i in range(B)])
+    assert not torch.equal(y2, y.detach())
+    with pytest.raises(NotImplementedError):
+        m.unfreeze_modality_embedder()
