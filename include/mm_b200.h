@@ -9,7 +9,9 @@
  * SM count, both behind atomics, and two environment switches read once at first use);
  * every call is re-entrant across host threads, streams and devices.  Scratch memory is
  * always caller-supplied, so two streams never share a buffer unless the caller hands
- * them the same one.  Return value: MM_OK or an
+ * them the same one.  (One documented exception to all three: mm_attach_positions_static,
+ * for callers that cannot allocate, keeps its scratch in a fixed array inside the library.)
+ * Return value: MM_OK or an
  * mm_status error (host-detectable argument errors).  Data-dependent errors (an
  * index out of range, attachment-token count != number of modality rows) are
  * reported through the caller-supplied device `status` word (see mm_status_bits) so
@@ -82,6 +84,39 @@ int mm_attach_positions(const int64_t* input_ids, int64_t n_ids, int64_t attachm
                         int32_t* dest_rows, int64_t n_rows_cap, int32_t* src_of_pos,
                         int32_t* count, int64_t expected_rows, int32_t* status,
                         void* workspace, void* stream);
+
+/*
+ * mm_attach_positions_static — mm_attach_positions for callers that cannot allocate device memory.
+ * No counterpart in the reference: it exists only because of how this library may be hosted.
+ *
+ * Who needs it: a host process that handed all of HBM to its own pool at start-up and may not call
+ * cudaMalloc afterwards (inference servers commonly work this way), a plugin or foreign-language
+ * binding that receives device pointers for the inputs and outputs but has no allocator of its own,
+ * or any caller that wants this step to have a fixed, known memory footprint.  Such a caller cannot
+ * produce the `workspace` argument of mm_attach_positions, so this variant drops it.
+ *
+ * Same inputs, outputs, status bits and results as mm_attach_positions (the same three kernels run).  The
+ * per-block counters live in a fixed array inside the library image (MM_ATTACH_STATIC_MAX_IDS / 2048
+ * int32 = 32 KB, 256-byte aligned) which every GPU that loads the library keeps until the process
+ * exits.  The call itself allocates and frees nothing — no cudaMalloc, no cudaFree, no library
+ * routine that allocates.
+ *
+ *   limit     n_ids <= MM_ATTACH_STATIC_MAX_IDS, otherwise MM_ERR_BAD_ARG and nothing is launched.
+ *             Longer id vectors need mm_attach_positions with a caller-owned workspace.
+ *   set-up    the first call on each device (the device that is current, which must be the one
+ *             `stream` belongs to) looks up the array's device address with cudaGetSymbolAddress
+ *             and remembers it.  Make that first call outside any stream capture.
+ *   sharing   every call on a device uses the same array and the array keeps whatever the last
+ *             call left in it.  Nothing needs to start at zero (each counter is written before it is
+ *             read), so back-to-back calls on one stream are fine.  Two calls that can run at the
+ *             same time on one GPU — different streams, or different host threads on different
+ *             streams — race on the array and return garbage: order them yourself (one stream, or
+ *             events), or give the concurrent ones mm_attach_positions with their own workspace.
+ */
+#define MM_ATTACH_STATIC_MAX_IDS 16777216 /* 2^24 ids, e.g. 2048 sequences of 8192 tokens */
+int mm_attach_positions_static(const int64_t* input_ids, int64_t n_ids, int64_t attachment_id,
+                               int32_t* dest_rows, int64_t n_rows_cap, int32_t* src_of_pos,
+                               int32_t* count, int64_t expected_rows, int32_t* status, void* stream);
 
 /*
  * mm_splice_scatter — embedded[dest_rows[k], :] = src[k, :]  (with dtype cast).

@@ -26,6 +26,7 @@ SIGNATURES = {
     "mm_device_sm_count": (i32, [i32]),
     "mm_attach_positions_workspace_bytes": (i64, [i64]),
     "mm_attach_positions": (i32, [vp, i64, i64, vp, i64, vp, vp, i64, vp, vp, vp]),
+    "mm_attach_positions_static": (i32, [vp, i64, i64, vp, i64, vp, vp, i64, vp, vp]),
     "mm_splice_scatter": (i32, [vp, i64, i64, i32, vp, i64, i32, vp, vp, vp]),
     "mm_splice_scatter_idx": (i32, [vp, i64, i64, i64, i32, vp, i64, i32, vp, vp, vp, vp]),
     "mm_embed_splice_fused": (i32, [vp, i64, i64, i32, vp, i64, vp, vp, vp, i64, i32, vp, vp]),

@@ -415,6 +415,49 @@ extern "C" int mm_attach_positions(const int64_t* input_ids, int64_t n_ids, int6
   return MM_OK;
 }
 
+// ---- mm_attach_positions_static: the same prefix sum for hosts that cannot allocate device memory -------
+// Some hosts of this library have no way to get scratch memory on the GPU: a serving runtime that reserved
+// all of HBM for its own pool at start-up and forbids cudaMalloc afterwards, a plugin that is handed raw
+// device pointers for the inputs and outputs but owns no allocator, a binding from a language where the
+// only CUDA the caller sees is this library.  For them the per-block attachment counters live in the array
+// below, which is part of the library image: every GPU that loads libmm_b200.so holds these 32 KB until the
+// process exits, and no call here allocates or frees anything.
+//
+// In HOST code `g_attach_static_scratch` is only a handle for the symbol, not an address the GPU can use —
+// passing it to a kernel would fault (or quietly hit host memory on systems where the GPU can reach it).  The
+// device address is looked up with cudaGetSymbolAddress, once per device, with that device current, and
+// remembered in g_attach_static_ptr[device].
+constexpr int64_t kAttachStaticMaxBlocks = MM_ATTACH_STATIC_MAX_IDS / kScanChunk;
+static_assert(kAttachStaticMaxBlocks * kScanChunk == MM_ATTACH_STATIC_MAX_IDS, "limit must be whole scan chunks");
+static __device__ __align__(256) int32_t g_attach_static_scratch[kAttachStaticMaxBlocks];
+constexpr int kAttachStaticMaxDevices = 64;
+static std::atomic<int32_t*> g_attach_static_ptr[kAttachStaticMaxDevices];
+
+extern "C" int mm_attach_positions_static(const int64_t* input_ids, int64_t n_ids, int64_t attachment_id,
+                                          int32_t* dest_rows, int64_t n_rows_cap, int32_t* src_of_pos,
+                                          int32_t* count, int64_t expected_rows, int32_t* status, void* stream) {
+  // the array has room for MM_ATTACH_STATIC_MAX_IDS ids and cannot grow: say so instead of running past it
+  if (n_ids < 0 || n_ids > MM_ATTACH_STATIC_MAX_IDS) return MM_ERR_BAD_ARG;
+  int dev = -1;
+  MM_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kAttachStaticMaxDevices) return MM_ERR_BAD_ARG;
+  int32_t* scratch = g_attach_static_ptr[dev].load(std::memory_order_acquire);
+  if (!scratch) {
+    // first call on this device: resolve the symbol to this device's copy of the array.  Two threads racing here
+    // get the same answer, so the unsynchronised store is harmless.
+    void* p = nullptr;
+    MM_CUDA_CHECK(cudaGetSymbolAddress(&p, g_attach_static_scratch));
+    if (!p) return MM_ERR_CUDA;
+    scratch = static_cast<int32_t*>(p);
+    g_attach_static_ptr[dev].store(scratch, std::memory_order_release);
+  }
+  // Nothing has to be cleared between calls: attach_count_kernel writes counter i of every block i < nblk before
+  // attach_scan_kernel / attach_write_kernel read it, and counters >= nblk are never read.  What the array keeps
+  // from the previous call is therefore invisible — as long as calls do not overlap on the GPU.
+  return mm_attach_positions(input_ids, n_ids, attachment_id, dest_rows, n_rows_cap, src_of_pos, count,
+                             expected_rows, status, scratch, stream);
+}
+
 extern "C" int mm_splice_scatter(void* dest, int64_t n_dest_rows, int64_t hidden, int dst_dtype, const void* src,
                                  int64_t n_rows, int src_dtype, const int32_t* dest_rows, int32_t* status,
                                  void* stream) {
