@@ -100,10 +100,17 @@ class SpliceRowsFunction(torch.autograd.Function):
     def backward(ctx, grad):
         (rows,) = ctx.saved_tensors
         g = grad.contiguous()
-        gsrc = ops.gather_rows(g, rows, out_dtype=g.dtype).to(ctx.src_dtype)
-        # positions overwritten by the splice carry no gradient back to the embedding rows (index_put_ semantics);
-        # the base tensor comes from a frozen table on this path, so its gradient is not materialised
-        return None, gsrc, None, None
+        gsrc = ops.gather_rows(g, rows, out_dtype=g.dtype).to(ctx.src_dtype) if ctx.needs_input_grad[1] else None
+        # index_put_ semantics for the base tensor: the rows this splice overwrote carry no gradient back to what was
+        # there before, every other row passes through.  The base needs that gradient when it is itself the output of
+        # an earlier splice whose source trains (two modality types with trainable projectors); a base gathered from
+        # the frozen table does not require grad and nothing is materialised for it.
+        gdest = None
+        if ctx.needs_input_grad[0]:
+            gdest = g.clone()
+            zeros = torch.zeros(rows.numel(), g.shape[-1], dtype=g.dtype, device=g.device)
+            ops.splice_scatter(gdest, zeros, rows)       # status=None: rows < 0 ("skip") are ignored, as in forward
+        return gdest, gsrc, None, None
 
 
 def splice_rows(dest2d: torch.Tensor, src: torch.Tensor, rows: torch.Tensor, status=None) -> torch.Tensor:

@@ -87,11 +87,18 @@ class B200MultiModalEmbedder(torch.nn.Module):
                                    f"indexing result of shape [{have}, {H}]")
 
     def embed_modalities_with_text(self, input_ids: torch.Tensor, processed_multimodal_inputs: Dict[str, Any],
-                                   positions_from: str = "collator", eager_checks: bool = True) -> torch.Tensor:
+                                   positions_from: str = "collator", eager_checks: bool = True,
+                                   skip_attachment_rows: Optional[bool] = None) -> torch.Tensor:
         """model.py:410-446.  positions_from:
           'collator' — use processed_multimodal_inputs['batch_idx'/'token_range'] as the reference does;
           'device'   — ignore them and derive the positions from input_ids with the device prefix sum
                        (valid for a single modality type); no index H2D at all.
+        skip_attachment_rows (device positions only): do not copy the attachment token's own embedding row into the
+          positions the splice overwrites anyway.  None (default) = only when the eager host check has just proved
+          that the attachment-token count matches the modality rows (host ids, eager_checks=True); with a lazy check
+          (device-resident ids or eager_checks=False) the rows ARE copied, so that on a count mismatch the result holds
+          real embedding rows like the reference's (model.py:433) rather than uninitialised memory until check()
+          raises.  True = the caller vouches for the counts and accepts that contract (bench.py's device-resident leg).
         Autograd: runs without a graph unless a modality's projector is trainable (`unfreeze_projection()`), in which
         case the projector and the splice are differentiable (autograd_ops); the embedding table is treated as frozen
         and a table that requires grad raises instead of losing its gradient silently."""
@@ -102,8 +109,11 @@ class B200MultiModalEmbedder(torch.nn.Module):
         if torch.is_grad_enabled() and self.embed_table.requires_grad:
             raise NotImplementedError("the embedding table requires grad: the B200 splice path does not produce that "
                                       "gradient (freeze the LLM, or run under torch.no_grad())")
-        if eager_checks and not input_ids.is_cuda:
+        host_checked = eager_checks and not input_ids.is_cuda
+        if host_checked:
             self._eager_host_checks(input_ids, stacks, positions_from)
+        if skip_attachment_rows is None:
+            skip_attachment_rows = host_checked
         ids = self._host_stager(dev).upload(input_ids)      # pageable host ids -> pinned staging -> async H2D
         st = self.status()
         B, S = ids.shape
@@ -112,7 +122,7 @@ class B200MultiModalEmbedder(torch.nn.Module):
                   for n in stacks}
         with torch.no_grad():
             # device positions cover exactly the ids == attachment_id rows: those need no embedding copy (:433)
-            skip = self.attachment_token_idx if (positions_from == "device" and stacks) else None
+            skip = self.attachment_token_idx if (positions_from == "device" and stacks and skip_attachment_rows) else None
             embedded = ops.embed_gather(self.embed_table.detach(), ids, status=st, skip_id=skip)   # :433
         for name, stack in stacks.items():
             modality = self._get_modality_by_name(name)

@@ -99,6 +99,31 @@ def test_embed_modalities_with_text_vs_oracle(side, table_dtype):
     assert (proj.float() - ref).abs().max().item() <= 2e-2 * ref.abs().max().item()
 
 
+def test_lazy_check_never_returns_uninitialised_rows():
+    """Device-resident ids with MORE attachment tokens than modality rows: the check is lazy, and until check() raises
+    the un-spliced attachment position must hold the attachment token's real embedding row (what the reference's
+    nn.Embedding wrote there, model.py:433), not whatever torch.empty returned."""
+    cfg = TOWERS["tiny"]
+    m, _ = _modality("tiny", 64, 3)
+    ids, pmi, att, _ = _make_batch(2, 64, 2, cfg, 300, 6, "right")
+    extra = (ids[1] != att).nonzero()[-1]
+    ids[1, extra] = att                         # one attachment token more than modality rows
+    table = torch.randn(300, 64, device=DEV).bfloat16()
+    e = B200MultiModalEmbedder(table, [m], att)
+    poison = torch.full((2 * 64 * 64 * 8,), float("nan"), device=DEV).bfloat16()
+    del poison                                  # the caching allocator hands these NaN bytes to the next torch.empty
+    out = e(ids.to(DEV), pmi, positions_from="device")
+    assert torch.equal(out[1, extra].squeeze(0), table[att])
+    assert not torch.isnan(out.float()).any()
+    with pytest.raises(RuntimeError):
+        e.check()
+    # the explicit opt-in keeps the old contract (rows untouched until the splice) — only the shape is promised
+    out = e(ids.to(DEV), pmi, positions_from="device", skip_attachment_rows=True)
+    assert out.shape == (2, 64, 64)
+    with pytest.raises(RuntimeError):
+        e.check()
+
+
 def test_count_mismatch_is_detected_not_truncated():
     cfg = TOWERS["tiny"]
     m, _ = _modality("tiny", 64, 3)

@@ -74,6 +74,86 @@ def test_gather_rows_is_the_scatter_backward():
         ops.raise_for_status(st)
 
 
+def test_chained_splices_keep_every_source_gradient():
+    """Two splices into one sequence (two modality types): the second one's base is the first one's output, so its
+    backward must hand the base a gradient (zero on the rows it overwrote) — checked against index_put_ autograd,
+    including a row both splices write (the later one wins, the earlier source gets zero there)."""
+    H, n_dest = 256, 600
+    g = torch.Generator(device=DEV).manual_seed(11)
+    base = torch.randn(n_dest, H, device=DEV, generator=g).bfloat16()
+    perm = torch.randperm(n_dest, device=DEV, generator=g)
+    r1, r2 = perm[:150].clone(), perm[150:260].clone()
+    r2[0] = r1[5]                                                     # overlap
+    s1 = torch.randn(150, H, device=DEV, generator=g).bfloat16()
+    s2 = torch.randn(110, H, device=DEV, generator=g).bfloat16()
+    w = torch.randn(n_dest, H, device=DEV, generator=g).bfloat16()
+
+    a1, a2 = s1.clone().requires_grad_(True), s2.clone().requires_grad_(True)
+    out = autograd_ops.splice_rows(base.clone(), a1, r1)
+    out = autograd_ops.splice_rows(out.view(2, n_dest // 2, H).view(n_dest, H), a2, r2)   # through views, like model.py
+    (out.float() * w.float()).sum().backward()
+
+    b1, b2 = s1.clone().requires_grad_(True), s2.clone().requires_grad_(True)
+    ref = base.clone()
+    ref = ref.index_put((r1,), b1)
+    ref = ref.index_put((r2,), b2)
+    (ref.float() * w.float()).sum().backward()
+    assert torch.equal(out.detach(), ref.detach())
+    assert a1.grad is not None and torch.equal(a1.grad, b1.grad)
+    assert torch.equal(a2.grad, b2.grad)
+    assert not a1.grad[5].any() and a1.grad[4].any()
+
+
+def test_two_trainable_modalities_alignment_step():
+    """ALIGNMENT stage with two modality types whose projectors both train (collator positions): each projector's
+    gradients against fp32 autograd through the oracle projector.  Before the fix the first-spliced modality's
+    projector silently received no gradient."""
+    cfg = TOWERS["tiny"]
+    H, V, B, S = 64, 300, 2, 64
+    att, P = V - 4, cfg.num_patches
+    mods, sds = [], []
+    for i, name in enumerate(("image", "scan")):
+        sd = synth.make_modality_state_dict(cfg, H, seed=20 + i)
+        m = AutoModality.from_config(AutoModality.config_from_dict(
+            {"model_type": "meditron_clip_b200", "hidden_size": H, "clip_name": "tiny"})).load_reference_state_dict(sd, DEV)
+        m.config.modality_type = name
+        mods.append(m)
+        sds.append(sd)
+    # per sequence: [text, P attachment tokens of "image", text, P attachment tokens of "scan", text]
+    assert 2 * P + 6 <= S
+    ids = torch.randint(0, V - 8, (B, S))
+    o1, o2 = 2, 2 + P + 2
+    ids[:, o1:o1 + P] = att
+    ids[:, o2:o2 + P] = att
+    px = [synth.make_pixels(cfg, B, seed=30 + i) for i in range(2)]
+    bidx = torch.arange(B).repeat_interleave(P)
+    pmi = {"stacked": {"image": [px[0][b] for b in range(B)], "scan": [px[1][b] for b in range(B)]},
+           "batch_idx": {"image": bidx, "scan": bidx.clone()},
+           "token_range": {"image": (o1 + torch.arange(P)).repeat(B), "scan": (o2 + torch.arange(P)).repeat(B)}}
+    table = (torch.randn(V, H, generator=torch.Generator().manual_seed(3)) * 0.02).bfloat16().to(DEV)
+    emb = B200MultiModalEmbedder(table, mods, att)
+    with torch.no_grad():
+        base = emb(ids, pmi, positions_from="collator").clone()
+    for m in mods:
+        m.unfreeze_projection()
+    out = emb(ids, pmi, positions_from="collator")
+    emb.check()
+    assert out.requires_grad and torch.equal(out.detach(), base)
+    w = torch.randn_like(out)
+    (out.float() * w.float()).sum().backward()
+    for i, (m, off) in enumerate(zip(mods, (o1, o2))):
+        with torch.no_grad():
+            feats = m.runner.features(px[i].to(DEV)).float()
+        p32 = {k: v.to(DEV).float().requires_grad_(True) for k, v in sds[i].items() if k.startswith("projector.")}
+        y = vit_oracle.mlp_projector(p32, feats)
+        y.backward(w[:, off:off + P].reshape(-1, H).float())
+        for k, p in m.named_parameters():
+            assert p.grad is not None, (m.config.modality_type, k)
+            r = p32[k].grad
+            err, scale = (p.grad.float() - r).abs().max().item(), r.abs().max().item()
+            assert err <= 3e-2 * scale + 1e-6, (m.config.modality_type, k, err, scale)
+
+
 def test_embed_gather_skip_leaves_attachment_rows_alone():
     V, H, att = 300, 256, 296
     table = torch.randn(V, H, device=DEV).bfloat16()
