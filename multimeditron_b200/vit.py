@@ -243,7 +243,18 @@ class GroupedTowerRunner:
         assert len(weights) > 1 and all(w.cfg == weights[0].cfg for w in weights) and FOLD_LN
         self.ws_list, self.cfg, self.E = weights, weights[0].cfg, len(weights)
         self.device = weights[0].device
-        cat = lambda key, i: torch.cat([w.layers[i][key] for w in weights], 0).contiguous()  # noqa: E731
+
+        def cat(key, i):
+            """Stack one parameter of all experts along its rows ONCE and make every expert's own entry a view (row
+            slice) of the stack: the per-expert runners (the fallback when `eligible()` says no) and the grouped path
+            then read the same storage, instead of the experts' weights being resident twice."""
+            parts = [w.layers[i][key] for w in weights]
+            stacked = torch.cat(parts, 0).contiguous()
+            n = parts[0].shape[0]
+            for e, w in enumerate(weights):
+                w.layers[i][key] = stacked[e * n:(e + 1) * n]      # contiguous, 16-byte aligned (n*K*2 B per expert)
+            return stacked
+
         self.layers = []
         for i in range(self.cfg.num_hidden_layers):
             L = {k: cat(k, i) for k in ("wo", "bo", "w2", "b2", "w1_f", "b1_f")}

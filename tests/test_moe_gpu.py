@@ -226,6 +226,14 @@ def test_grouped_experts_equal_per_expert_runners(monkeypatch):
     gate = lambda p: w[:p.shape[0]].to(p.device)     # noqa: E731
     m = AutoModality.from_config(mcfg).load_reference_state_dict(sd, DEV, gating=gate)
     assert m._grouped is not None and m._grouped.eligible(B)
+    # the experts' own weights are row slices of the stacked tensors (one resident copy, not two)
+    for i in (0, 1):
+        for k in ("wo", "w2", "w1_f", "wqkv" if i == 0 else "wqkv_f"):
+            stacked = m._grouped.layers[i][k]
+            n = stacked.shape[0] // E
+            for e in range(E):
+                mine = m._runners[e].w.layers[i][k]
+                assert mine.data_ptr() == stacked[e * n].data_ptr() and mine.shape[0] == n and mine.is_contiguous()
     y = m(px)
     monkeypatch.setenv("MM_B200_MOE_GROUPED", "0")
     m2 = AutoModality.from_config(mcfg).load_reference_state_dict(sd, DEV, gating=gate)
