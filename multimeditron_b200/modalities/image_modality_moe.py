@@ -320,6 +320,10 @@ class _B200MOEBase(BaseModality):
                 done.record(self._gate_stream)
             self._grouped.features(px, stack)
             cur.wait_event(done)
+            # w was allocated from the gate stream's pool but is consumed on `cur`: tell the caching allocator, so the
+            # block cannot be handed out again on the gate stream before cur's readers have run (today the next use of
+            # the gate stream waits on a fork event recorded after them, but callers need not keep to that pattern)
+            w.record_stream(cur)
             self._joins = None
             return w
         self._each_expert(lambda e, r: r.features(px, out=stack[e]))
