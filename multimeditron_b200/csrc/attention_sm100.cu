@@ -33,26 +33,23 @@ constexpr int kMaxStages = 8;
 #define MM_ATTN_POLL_NS 32
 #endif
 constexpr unsigned kPollSleepNs = MM_ATTN_POLL_NS;  // idle back-off of the two polling service threads
-// MM_ATTN_TOKEN=1: the two streams take turns in the exp phase (named-barrier token).  Measured (tools/micro/
-// tmem_probe2): a lone warp per scheduler sustains 10.5 clk per ex2, two interleaved warps 8.7 — so the default lets
-// both streams run their exp phases freely and the token survives only as an A/B switch.
+// MM_ATTN_TOKEN (default 1 = ON, the build that ships and that every test and bench number comes from): the two
+// streams take turns in the exp phase — a named-barrier token passed between the two softmax warps that share a
+// scheduler — so one stream's exps run while the other stream's S tile is produced.  -DMM_ATTN_TOKEN=0 lets both
+// streams exponentiate whenever they like; kept as an A/B switch only (a micro-benchmark, tools/micro/tmem_probe2,
+// had two interleaved warps at 8.7 clk per ex2 against 10.5 for a lone warp, but in the whole kernel the token's
+// regular hand-over wins).
 #ifndef MM_ATTN_TOKEN
 #define MM_ATTN_TOKEN 1
 #endif
-// MM_ATTN_STALE_MAX=1: from the second kv tile on, the exps of a tile use the reference max decided by the PREVIOUS
-// tiles (known before S even arrives); the tile's own row max is computed next to the exps (FMNMX3 on the ALU pipe,
-// hidden under the MUFU-bound exp stream) and only feeds the NEXT tile's decision.  P <= 2^kRedoThreshold is
-// harmless (bf16 P and the fp32 O / row sum have the exponent range); beyond it the tile's exps are redone with the
-// tile max (never taken on real data: the reference already is a max over >= 128 keys).
-#ifndef MM_ATTN_STALE_MAX
-#define MM_ATTN_STALE_MAX 0
-#endif
+// Every kv tile decides its reference max from ITS OWN scores before its exps run.  (A "stale max" variant, which
+// took the reference from the previous tiles and re-exponentiated a tile whose scores jumped past it, was measured
+// in round 2, never shipped, and has been removed.)
 // MM_ATTN_PACKED=1: the scale-and-shift before each ex2 and the row-sum adds run as packed fp32x2 instructions
 // (FFMA2 / FADD2): 2.5 instead of 3.5 issue slots per score in the exp phase.
 #ifndef MM_ATTN_PACKED
 #define MM_ATTN_PACKED 1
 #endif
-constexpr float kRedoThreshold = 60.0f;   // log2 units
 
 template <int HD, int BKV>
 struct AttnCfg {
@@ -500,7 +497,6 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         const int qt = sc.first_qt(s, g) + 2 * j;
         const bool warp_live = qt * kBQ + q * 32 < p.T;  // warps whose 32 rows are all padding only keep the protocol
         float m_run = -INFINITY, l_run = 0.f;            // running max (raw score units) and row sum
-        float m_next = -INFINITY;                        // reference max the NEXT kv tile will use (stale-max mode)
         for (int kt = 0; kt < nkv; ++kt, ++it) {
           const int valid = p.T - kt * BKV;  // columns >= valid are padding (only in the last kv tile)
           sm_wait(&bars->s_full[s], it & 1);
@@ -521,28 +517,23 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
           uint32_t pk[BKV / 2];
           float m_new = m_run, sum = 0.f;
           float m_scaled = 0.f;
-          const bool stale = MM_ATTN_STALE_MAX && kt > 0;   // reference max already decided by the previous tiles
           if (warp_live) {
             if (valid < BKV) {
 #pragma unroll
               for (int jj = 0; jj < BKV; ++jj)
                 if (jj >= valid) sv[jj] = 0xff800000u;  // -inf
             }
-            if (!stale) {
-              float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+            float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-              for (int jj = 0; jj < BKV; jj += 8) {
-                mx0 = fmaxf(mx0, fmaxf(__uint_as_float(sv[jj + 0]), __uint_as_float(sv[jj + 1])));
-                mx1 = fmaxf(mx1, fmaxf(__uint_as_float(sv[jj + 2]), __uint_as_float(sv[jj + 3])));
-                mx2 = fmaxf(mx2, fmaxf(__uint_as_float(sv[jj + 4]), __uint_as_float(sv[jj + 5])));
-                mx3 = fmaxf(mx3, fmaxf(__uint_as_float(sv[jj + 6]), __uint_as_float(sv[jj + 7])));
-              }
-              const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-              // the reference max only moves when it grows by more than the threshold (keeps O rescales rare)
-              if ((mx - m_run) * sl2 > kRescaleThreshold) m_new = mx;  // also true for m_run = -inf
-            } else {
-              m_new = m_next;
+            for (int jj = 0; jj < BKV; jj += 8) {
+              mx0 = fmaxf(mx0, fmaxf(__uint_as_float(sv[jj + 0]), __uint_as_float(sv[jj + 1])));
+              mx1 = fmaxf(mx1, fmaxf(__uint_as_float(sv[jj + 2]), __uint_as_float(sv[jj + 3])));
+              mx2 = fmaxf(mx2, fmaxf(__uint_as_float(sv[jj + 4]), __uint_as_float(sv[jj + 5])));
+              mx3 = fmaxf(mx3, fmaxf(__uint_as_float(sv[jj + 6]), __uint_as_float(sv[jj + 7])));
             }
+            const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+            // the reference max only moves when it grows by more than the threshold (keeps O rescales rare)
+            if ((mx - m_run) * sl2 > kRescaleThreshold) m_new = mx;  // also true for m_run = -inf
             m_scaled = m_new * sl2;
           }
           TRACE_SM(14);
@@ -553,31 +544,18 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
           if (warp_live) {
             ExpAcc ea;
             exp_acc_reset(ea);
-            float tx0 = -INFINITY, tx1 = -INFINITY;   // this tile's own row max (feeds the next tile's decision)
             if (valid >= BKV) {
               // full tile: one straight-line block, so that ptxas interleaves the ex2 of the whole row (a block per
               // 32-column chunk drains the MUFU pipe at every boundary: measured 1900 vs 1250 clk per tile)
 #pragma unroll
-              for (int jj = 0; jj < BKV; jj += 4) {
-                exp4(sv + jj, pk + (jj >> 1), sl2, m_scaled, ea);
-                if (MM_ATTN_STALE_MAX) {
-                  tx0 = fmaxf(tx0, fmaxf(__uint_as_float(sv[jj + 0]), __uint_as_float(sv[jj + 1])));
-                  tx1 = fmaxf(tx1, fmaxf(__uint_as_float(sv[jj + 2]), __uint_as_float(sv[jj + 3])));
-                }
-              }
+              for (int jj = 0; jj < BKV; jj += 4) exp4(sv + jj, pk + (jj >> 1), sl2, m_scaled, ea);
             } else {
               // last (partial) kv tile: chunks that are all padding are skipped
 #pragma unroll
               for (int c = 0; c < NCH; ++c) {
                 if (c * 32 < valid) {
 #pragma unroll
-                  for (int jj = c * 32; jj < c * 32 + 32; jj += 4) {
-                    exp4(sv + jj, pk + (jj >> 1), sl2, m_scaled, ea);
-                    if (MM_ATTN_STALE_MAX) {
-                      tx0 = fmaxf(tx0, fmaxf(__uint_as_float(sv[jj + 0]), __uint_as_float(sv[jj + 1])));
-                      tx1 = fmaxf(tx1, fmaxf(__uint_as_float(sv[jj + 2]), __uint_as_float(sv[jj + 3])));
-                    }
-                  }
+                  for (int jj = c * 32; jj < c * 32 + 32; jj += 4) exp4(sv + jj, pk + (jj >> 1), sl2, m_scaled, ea);
                 } else {
 #pragma unroll
                   for (int jj = 0; jj < 16; ++jj) pk[c * 16 + jj] = 0u;
@@ -585,20 +563,6 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
               }
             }
             sum = exp_acc_total(ea);
-            if (MM_ATTN_STALE_MAX) {
-              const float tx = fmaxf(tx0, tx1);
-              const float over = (tx - m_new) * sl2;   // how far this tile's own max sits above the reference used
-              m_next = over > kRescaleThreshold ? tx : m_new;
-              if (stale && __any_sync(0xffffffffu, over > kRedoThreshold)) {
-                // the stale reference was far too low for this tile (P would leave the safe range): redo the row
-                // with the tile max — rows below the redo threshold keep their reference (identical results)
-                if (over > kRedoThreshold) m_new = tx, m_scaled = tx * sl2;
-                exp_acc_reset(ea);
-#pragma unroll
-                for (int jj = 0; jj < BKV; jj += 4) exp4(sv + jj, pk + (jj >> 1), sl2, m_scaled, ea);
-                sum = exp_acc_total(ea);
-              }
-            }
           }
           TRACE_SM(2);
 #if MM_ATTN_TOKEN

@@ -249,9 +249,12 @@ def test_attention_peaked_rows_rescale():
 
 @pytest.mark.parametrize("T,hd,jump_at", [(577, 64, 256), (577, 64, 130), (729, 72, 480), (300, 64, 290)])
 def test_attention_score_jump_beyond_the_stale_reference(T, hd, jump_at):
-    """From the second kv tile on the exps use the reference max decided by the EARLIER tiles (stale max).  Here the
-    scores jump by > 100 log2 units at key `jump_at`: rows must take the redo path (tile re-exponentiated with its own
-    max) instead of overflowing, and rows whose jump stays below the redo threshold must rescale on the next tile."""
+    """Online softmax under a sudden score jump.  The running reference max only moves when a kv tile's own max exceeds
+    it by more than the lazy-rescale threshold (2^8); here the scores jump by > 100 log2 units at key `jump_at` (first
+    image) and by a quarter of that (second image), in the middle of a kv tile and near the end of the row: the O
+    accumulator and the row sum must be rescaled at that tile, and nothing may overflow.  (The name is historical: a
+    'stale max' variant of the kernel, removed in round 3, motivated the case; the shipped kernel — head_dim 64 through
+    attention3_sm100.cu, head_dim 72 through attention_sm100.cu — decides every tile's max from its own scores.)"""
     B, nh = 2, 2
     hs = ops.attn_head_stride(hd)
     g0 = torch.Generator().manual_seed(T + hd)
