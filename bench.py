@@ -48,6 +48,13 @@ GLOBAL_BATCH = {"cfg1_clip_b32_tiny_llama": 8, "cfg2_clip_l14_336_llama8b": 256,
 # cfg2 B=256 (profiles/r02_ncu_full_summary.txt, round 2 code): GEMM = mean over one encoder layer's four launches
 # (fc2+stats 1.847, qkv(LN folded) 1.184, out-proj+stats 0.883, fc1(LN folded) 1.486 GB); attention3 1.183 GB.
 NCU_TRAFFIC = {"cfg2_clip_l14_336_llama8b": {"gemm": 1.350e9, "attention": 1.1833e9, "layernorm": 0.5464e9}}
+# the two standalone splice passes, from the round-3 `--set full` capture of tools/splice_roofline.py (same shapes as the
+# loops below; profiles/r03_ncu_splice.txt): scatter 1.2088 GB read + 1.1616 GB written for 2.416 GB algorithmic,
+# fused embed+splice 4.2237 + 4.2434 GB for 8.590 GB — no re-reads; the part of the last writes that is still in the
+# 126 MB L2 when the kernel ends accounts for the 1.5-2 % below algorithmic.
+NCU_TRAFFIC_SPLICE = {"scatter_cfg2": 2.3703e9, "embed_splice_cfg4": 8.4671e9}
+# spec-sheet peaks (dense bf16 tensor, HBM3e) — SURVEY §8 D3 asks for the fraction of these next to the measured ones
+SPEC_TF, SPEC_HBM_GBS = 2250.0, 8000.0
 
 
 def workload(wl):
@@ -180,7 +187,61 @@ def cpu_reference_leg(wl, sample_images, steps, warmup, threads, dtype_name="flo
     return toks, dt_s * 1e3, desc
 
 
-def cpu_baseline_block(wl, sample_images, threads, steps=5, warmup=2, budget_s=45.0):
+def cpu_unmodified_reference_leg(wl, sample_images, steps, warmup, threads, dtype_name, budget_s=None):
+    """The UNMODIFIED reference on the host cores: the reference's own `MultiModalModelForCausalLM`
+    (oracle/_ref staging, or /root/reference in the build container) with its stock `meditron_clip` ImageModality built
+    from a random-init HF CLIP checkpoint of the workload's tower and a 1-layer Llama config of the workload's hidden size
+    and vocabulary; the timed call is its own `embed_modalities_with_text` (model.py:410-446) on the collator's format.
+    Same sample, same best-of reporting as the port leg.  Raises if the reference is not staged."""
+    import shutil
+
+    import torch
+    from multimeditron_b200 import synth
+    from multimeditron_b200.configs import TOWERS
+    from oracle import ref_harness, ref_shim, splice_oracle
+    ref = ref_shim.import_reference()
+    torch.set_num_threads(threads)
+    cfg, H, V, S, att, ids, px = build_inputs(wl, 0, sample_images, torch, synth, TOWERS)
+    per_row = workload(wl)["per_row"]
+    clip_dir = ref_harness.save_clip_checkpoint(cfg, seed=0)
+    llama_dir = ref_harness.save_tiny_llama(V, hidden=H, layers=1, heads=max(1, H // 128))
+    try:
+        mcfg = ref.modalities.AutoModality.config_from_dict(dict(model_type="meditron_clip", hidden_size=H,
+                                                                 clip_name=clip_dir))
+        rcfg = ref.model.MultimodalConfig(vocab_size=V, modalities=[mcfg], pad_token_idx=V - 1, eos_token_idx=V - 1,
+                                          padding_side="right", llm_path=llama_dir, dtype=dtype_name)
+        torch.manual_seed(0)
+        model = ref.model.MultiModalModelForCausalLM(rcfg).to(getattr(torch, dtype_name)).eval()
+    finally:
+        shutil.rmtree(clip_dir, ignore_errors=True)
+        shutil.rmtree(llama_dir, ignore_errors=True)
+    ranges = [splice_oracle.compute_token_range(ids[b].numpy(), [cfg.num_patches] * per_row, att)
+              for b in range(ids.shape[0])]
+    bidx, trng = map(torch.from_numpy, splice_oracle.collator_indices(ranges))
+    pmi = {"stacked": {"image": [px[i] for i in range(sample_images)]}, "batch_idx": {"image": bidx},
+           "token_range": {"image": trng}}
+
+    def step():
+        with torch.no_grad():
+            return model.embed_modalities_with_text(ids, pmi)
+
+    for _ in range(warmup):
+        step()
+    times, t_begin = [], time.perf_counter()
+    for i in range(steps):
+        t0 = time.perf_counter()
+        step()
+        times.append(time.perf_counter() - t0)
+        if budget_s is not None and i >= 4 and time.perf_counter() - t_begin > budget_s:
+            break
+    dt_s = min(times)
+    desc = (f"{sample_images} of {WORKLOADS[wl][2]} images per step ({dtype_name}, the unmodified reference's "
+            f"MultiModalModelForCausalLM.embed_modalities_with_text with its stock meditron_clip modality, {threads} threads, "
+            f"best of {len(times)} after {warmup} warm-ups)")
+    return sample_images * cfg.num_patches / dt_s, dt_s * 1e3, desc
+
+
+def cpu_baseline_block(wl, sample_images, threads, steps=5, warmup=2, budget_s=45.0, unmodified=False):
     """fp32 AND bf16, 8 images, 2 warm-ups, best of 5.  The headline `value` is the FASTER of the two
     (bf16 on hosts with AMX/AVX512-BF16, fp32 elsewhere) so that the GPU/CPU ratio is not flattered."""
     res = {}
@@ -189,9 +250,20 @@ def cpu_baseline_block(wl, sample_images, threads, steps=5, warmup=2, budget_s=4
                                            budget_s=budget_s)
         res[dn] = dict(value=toks, ms_per_step=ms, sample=desc)
     best = max(res, key=lambda k: res[k]["value"])
-    return {"value": res[best]["value"], "unit": UNIT, "cores": threads, "kind": "port", "dtype": best,
-            "sample": res[best]["sample"], "fp32": res["float32"]["value"], "bf16": res["bfloat16"]["value"],
-            "note": "one host (rank 0) only: at N>1 the ratio is N GPUs over one host's cores"}
+    out = {"value": res[best]["value"], "unit": UNIT, "cores": threads, "kind": "port", "dtype": best,
+           "sample": res[best]["sample"], "fp32": res["float32"]["value"], "bf16": res["bfloat16"]["value"],
+           "statistic": "best single step (not the mean): conservative for the GPU/CPU ratio, the GPU arm reports the mean",
+           "note": "one host (rank 0) only: at N>1 the ratio is N GPUs over one host's cores"}
+    if unmodified:
+        # `--impl reference`: the unmodified reference itself (staged under oracle/_ref) in the dtype the port found faster;
+        # it becomes the headline when it runs, the port's figures stay beside it
+        try:
+            toks, ms, desc = cpu_unmodified_reference_leg(wl, sample_images, max(5, steps), max(2, warmup), threads, best,
+                                                          budget_s=budget_s)
+            out.update(port_value=out["value"], port_sample=out["sample"], value=toks, sample=desc, kind="reference")
+        except Exception as e:  # noqa: BLE001 — reference not staged / cannot be built on this box: keep the port
+            out["reference_unavailable"] = f"{type(e).__name__}: {e}"[:300]
+    return out
 
 
 def torch_gpu_leg(wl, images, steps, warmup, dev, seed=100):
@@ -320,15 +392,35 @@ def run_torch_gpu(args):
     emit(line)
 
 
+def config_block(wl, images, world, px_bytes=None):
+    """The `config` object of the JSON line — built from the workload's constants only, so that the B200 arm and the
+    `--impl reference` arm print the SAME object (the driver compares them)."""
+    from multimeditron_b200.configs import TOWERS
+    w = workload(wl)
+    cfg = TOWERS[w["tower"]]
+    P, H = cfg.num_patches, w["H"]
+    S = w["seq_len"] or P + 2 + w["n_text"]
+    rows = images // w["per_row"]
+    if px_bytes is None:
+        px_bytes = images * 3 * cfg.image_size * cfg.image_size * 4
+    return {"workload": wl, "tower": w["tower"], "llm_hidden": H, "images_per_gpu": images,
+            "global_images": images * world, "rows_per_gpu": rows, "seq_len": S, "tokens_per_image": P,
+            "parallelism": f"sample-shard x{world}",
+            "l2": "inputs larger than L2 (pixels %.0f MB, inputs_embeds %.0f MB per step)" % (px_bytes / 1e6, rows * S * H * 2 / 1e6),
+            "positions": "device prefix sum", "splice": "fused into the last projector GEMM epilogue"}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
     sample = args.cpu_sample
-    # the driver's --steps/--warmup are for the GPU arm; the CPU arm follows BASELINE.md §4 (2 warm-ups, best of 5,
-    # fp32 and bf16) on a bounded sample so that the run ends within minutes
-    cb = cpu_baseline_block(args.workload, sample, threads, steps=args.steps, warmup=min(args.warmup, 3), budget_s=60.0)
+    # BASELINE.md §4: fp32 and bf16 on a bounded sample (8 images per step), the driver's --warmup (2..10) and --steps
+    # (at least 5, cut short by a 45 s budget per leg), best single step reported; then the unmodified reference itself
+    # (oracle/_ref) in the faster dtype — that one is the line's value when it runs, the port is the fallback
+    cb = cpu_baseline_block(args.workload, sample, threads, steps=args.steps, warmup=min(args.warmup, 10), budget_s=45.0,
+                            unmodified=True)
     toks, ms = cb["value"], 1e3 * sample * TOWERS_P(args.workload) / cb["value"]
     w = workload(args.workload)
     tower, H, ipg, n_text, V = w["tower"], w["H"], w["images"], w["n_text"], w["V"]
@@ -336,8 +428,9 @@ def run_reference(args):
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": {"float32": "f32", "bfloat16": "bf16"}[cb["dtype"]],
             "data": "synthetic (seeded N(0,1) pixels, random-init weights)",
-            "config": {"workload": args.workload, "tower": tower, "llm_hidden": H, "images_per_gpu": ipg,
-                       "sample": cb["sample"]},
+            # the B200 arm's config, verbatim (its GPU-side notes included): this arm is the same workload on the host cores,
+            # on a bounded sample of it that cpu_baseline.sample describes
+            "config": config_block(args.workload, args.images_per_gpu or ipg, max(1, args.gpus)),
             "cpu_baseline": cb,
             "e2e": {"value": toks, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -572,6 +665,25 @@ def run_b200(args):
     ms_sp = timed(lambda: ops.splice_scatter(emb.view(-1, H), proj, dest_rows), max(10, args.steps))
     splice_bytes = 2.0 * images * P * H * 2
     del proj, emb
+    # ---- fused embed + splice standalone (SURVEY D5 secondary) at cfg4's shape: inputs_embeds [64, 8192, H] bf16 written in
+    # ONE pass from ids, the table and the projected stack (mm_embed_splice_fused); 4 images x 576 tokens per sequence
+    es = None
+    if rank == 0 and not E:
+        Bs4, S4, per4, P4 = 64, 8192, 4, 576
+        ids4, _ = synth.make_sequences(Bs4, S4, per4, P4, V - 4, att, V - 4, V - 3, V - 1, seed=77)
+        ids4 = ids4.to(dev)
+        src4 = torch.randn(Bs4 * per4 * P4, H, device=dev).bfloat16()
+        _, sop4, _ = ops.attach_positions(ids4, att, expected_rows=src4.shape[0], want_src_of_pos=True)
+        out4 = torch.empty(Bs4, S4, H, dtype=torch.bfloat16, device=dev)
+        for _ in range(2):
+            ops.embed_splice_fused(table, ids4, sop4, src4, out=out4)
+        ms_es = timed(lambda: ops.embed_splice_fused(table, ids4, sop4, src4, out=out4), max(5, args.steps // 2))
+        es_bytes = 2.0 * Bs4 * S4 * H * 2
+        es = {"kernel": "move_rows_kernel<2> (mm_embed_splice_fused, standalone, cfg4 shape: 64 x 8192 x %d bf16)" % H,
+              "bound": "hbm", "achieved": es_bytes / (ms_es * 1e-3) / 1e9, "unit": "GB/s", "bytes": es_bytes, "ms": ms_es,
+              "traffic": NCU_TRAFFIC_SPLICE["embed_splice_cfg4"] if H == 4096 else None,
+              "traffic_src": "ncu --set full of tools/splice_roofline.py (profiles/r03_ncu_splice.txt)"}
+        del ids4, src4, sop4, out4
 
     gate_ms = None
     if E:
@@ -595,11 +707,7 @@ def run_b200(args):
         "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
         "dtype": "bf16", "data": ("real photographs (mock_dataset) through the HF image processor, random-init weights" if args.real_images else
                                   "synthetic (seeded N(0,1) pixels, random-init weights; no network for checkpoints)"),
-        "config": {"workload": args.workload, "tower": tower, "llm_hidden": H, "images_per_gpu": images,
-                   "global_images": total_images, "rows_per_gpu": ids.shape[0], "seq_len": S, "tokens_per_image": P, "parallelism": f"sample-shard x{world}",
-                   "l2": "inputs larger than L2 (pixels %.0f MB, inputs_embeds %.0f MB per step)" % (
-                       px.numel() * px.element_size() / 1e6, ids.shape[0] * S * H * 2 / 1e6),
-                   "positions": "device prefix sum", "splice": "fused into the last projector GEMM epilogue"},
+        "config": config_block(args.workload, images, world, px_bytes=px.numel() * px.element_size()),
         "clocks": clocks,
         "e2e": {"value": total_images * P / ((ms_e2e_list or ms_e2e) * 1e-3), "unit": UNIT,
                 "ms_per_step": ms_e2e_list or ms_e2e,
@@ -629,17 +737,27 @@ def run_b200(args):
                      "traffic_src": "ncu --set full, mean bytes per launch over one encoder layer's 4 GEMMs "
                                     "(profiles/r02_ncu_full_summary.txt)",
                      "peak_kind": f"{pk['src']} sustained cuBLAS bf16 (kernel timed inside a long step)",
-                     "frac_of_burst": gemm_tf / pk["tf_burst"]},
+                     "frac_of_burst": gemm_tf / pk["tf_burst"], "frac_of_spec": gemm_tf / SPEC_TF},
         "path_tensor": {"achieved": path_tf, "unit": "TFLOP/s", "frac_of_sustained": path_tf / pk["tf_sust"],
-                        "frac_of_burst": path_tf / pk["tf_burst"], "gflop_per_image": flops_img / 1e9,
+                        "frac_of_burst": path_tf / pk["tf_burst"], "frac_of_spec": path_tf / SPEC_TF,
+                        "gflop_per_image": flops_img / 1e9,
                         "note": "algorithmic FLOPs of the whole path / whole step time (attention, LN, patch, splice included)"},
         "roofline_splice": {"kernel": "move_rows_kernel<0> (mm_splice_scatter, standalone)", "bound": "hbm",
                             "achieved": splice_bytes / (ms_sp * 1e-3) / 1e9, "peak": pk["hbm"], "unit": "GB/s",
                             "frac": splice_bytes / (ms_sp * 1e-3) / 1e9 / pk["hbm"], "bytes": splice_bytes,
-                            "ms": ms_sp, "traffic": None},
+                            "ms": ms_sp, "frac_of_spec": splice_bytes / (ms_sp * 1e-3) / 1e9 / SPEC_HBM_GBS,
+                            "traffic": (NCU_TRAFFIC_SPLICE["scatter_cfg2"]
+                                        if (images, P, H) == (256, 576, 4096) else None),
+                            "traffic_src": "ncu --set full of tools/splice_roofline.py, same shape "
+                                           "(profiles/r03_ncu_splice.txt)"},
         "op_ms_per_step": {k: v[1] / args.steps for k, v in sorted(prof.items())},
         "roofline_attention": attention_roofline(cfg, images * (E or 1), prof, args.steps, clocks),
     }
+    if es is not None:
+        es["peak"] = pk["hbm"]
+        es["frac"] = es["achieved"] / pk["hbm"]
+        es["frac_of_spec"] = es["achieved"] / SPEC_HBM_GBS
+        line["roofline_embed_splice"] = es
     if E:
         line["config"]["experts"] = E
         line["config"]["inputs"] = "raw uint8 images, sizes drawn from {224,336,512,1024}^2, resized on the device"

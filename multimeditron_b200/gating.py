@@ -3,9 +3,11 @@
 callers, image_modality_moe.py:156, image_modality_moe_pep.py:194) and softmax weights.
 
 SURVEY.md §8(f) rank 3 / row A12: the gate is on the path of BASELINE configs[4] but is not one of the kernels
-`north_star` names; it runs through torchvision on cuDNN here (LIBRARY code, stated as such in DESIGN.md and in the
-bench line's `config.gating`), in bf16 channels-last.  It takes the same `[B,3,224,224]` pixel tensor the experts get and
-is launched on the caller's stream while the experts run on their side streams, so it overlaps them.
+`north_star` names.  Two implementations live here: `B200ResNet50Gate`, the default — the network on this library's
+own kernels (csrc/conv_ops.cu row staging + the tcgen05 GEMM with BatchNorm and ReLU folded into its epilogue) — and
+`ResNet50Gate`, the same network through torchvision on cuDNN in bf16 channels-last (LIBRARY code; kept as the
+comparison partner; bench.py selects it with MM_B200_GATE=cudnn and names the choice in the bench line's `config.gating`).  Either takes the
+same `[B,3,224,224]` pixel tensor the experts get and overlaps them on its own stream.
 State-dict keys are the reference's: `resnet.*` (inside a MoE modality: `gating_network.resnet.*`)."""
 from __future__ import annotations
 

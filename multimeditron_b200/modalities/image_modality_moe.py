@@ -9,10 +9,12 @@ Reference behaviour reproduced:
   * `sequence_append`: [B,E,P,*] flattened to [B,E*P,*] (:167-169 / :206-209);
   * state-dict keys `experts.<i>.*` (HF CLIPVisionTransformer), `projector.projection.*` (shared) or
     `projectors.<i>.projection.*` (PEP), `gating_network.resnet.*`.
-The expert towers, projectors and the fusion run on the sm_100a kernels.  The gating network (ResNet-50,
-moe/gating.py:73-89) is NOT on the north-star path: it is a caller-supplied callable
-`gating(pixels[B,3,h,w]) -> weights[B,E]` (a torch module on cuDNN, or precomputed weights); `cross_attn` fusion is
-out of scope for this round and raises.
+The expert towers, projectors and all three fusions (`weighted_average`, `sequence_append`, `cross_attn` — the last
+one inference-only: its backward is not written and `unfreeze_projection()` raises for it) run on the sm_100a kernels.
+The gating network (ResNet-50, moe/gating.py:73-89) is handed in by the caller (`load_reference_state_dict(..., gating=)`
+or `set_gating`): normally a `gating.B200ResNet50Gate` built from the `gating_network.resnet.*` entries of the same state
+dict (row staging + tcgen05 GEMMs, BatchNorm/ReLU folded), but any callable `gating(pixels[B,3,h,w]) -> weights[B,E]`
+(a torch module, precomputed weights) is accepted.
 """
 from __future__ import annotations
 

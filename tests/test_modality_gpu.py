@@ -185,6 +185,19 @@ def test_full_size_cfg2_batch_independence_and_splice_placement():
     assert torch.equal(flat[~is_att], table[idsd[~is_att]])          # text rows untouched, bit-exact
 
 
+def test_full_size_siglip_so400m_batch_independence():
+    """BASELINE configs[2]'s tower at FULL size (SigLIP so400m-patch14-384 -> 3584, head_dim 72 on the two-stream
+    attention kernel, no CLS token): 64 images — an image's embeddings do not depend on the batch it travels in, bit-exact
+    against a batch of 3 (different tile schedules, same per-row arithmetic), and nothing overflows."""
+    cfg = TOWERS["siglip_so400m_384"]
+    m, _ = _modality("siglip_so400m_384", 3584, 0)
+    px = synth.make_pixels(cfg, 64, seed=13).to(DEV)
+    y = m(px)                                                        # [64, 729, 3584]
+    assert y.shape == (64, cfg.num_patches, 3584) and torch.isfinite(y.float()).all()
+    pick = [0, 31, 63]
+    assert torch.equal(y[pick], m(px[pick].contiguous()))
+
+
 def test_two_streams_and_two_host_threads_share_one_modality():
     """B4 / include/mm_b200.h: re-entrant across streams and host threads.  One modality instance is driven from two
     CUDA streams at once (launches interleaved by two Python threads, each with its own stream): per-stream activation

@@ -17,7 +17,11 @@ echo "gemm capture exit $?"
 ncu --set full --clock-control none --import-source on -k "regex:attention3_fwd|attention_fwd" -s 60 -c 2 \
     -o gpurun_out/${tag}_attn $FULL > gpurun_out/ncu_attn.log 2>&1
 echo "attn capture exit $?"
-ncu --set full --clock-control none --import-source on -k "regex:move_rows_kernel|layernorm_kernel|resize_" -s 6 -c 8 \
-    -o gpurun_out/${tag}_hbm $FULL > gpurun_out/ncu_hbm.log 2>&1
-echo "hbm capture exit $?"
+# HBM-bound splice kernels: a dedicated target (the step itself fuses the splice into the projector GEMM's epilogue), so the
+# capture cannot land on load-time launches of another kernel: launch 1 = embed gather, 2 = scatter warm-up, 3-4 = scatter
+# (move_rows_kernel<0>, cfg2 shape), 5-7 = fused embed+splice (move_rows_kernel<2>, cfg4 shape)
+python tools/splice_roofline.py > gpurun_out/${tag}_splice_plain.json 2> gpurun_out/splice_plain.err &&
+SPLICE_REPS=2 ncu --set full --clock-control none --import-source on -k regex:move_rows_kernel -s 2 -c 5 \
+    -o gpurun_out/${tag}_splice python tools/splice_roofline.py > gpurun_out/ncu_splice.log 2>&1
+echo "splice capture exit $?"
 ls -la gpurun_out
