@@ -85,6 +85,44 @@ def test_gemm_bias_act(M, N, K, bias, act, residual, rowmap):
         close(ops.gemm_bias_act(a, w, bs, act, residual=res), ref)
 
 
+@pytest.mark.parametrize("M,N,K,bias,residual", [
+    (1000, 1024, 1024, True, False),      # out-proj shape, pair kernel
+    (577, 4096, 1024, True, False),       # fc1 shape (no activation: the bound below is about the accumulation)
+    (300, 1024, 4096, False, True),       # fc2 shape: long k, residual add
+    (128, 1152, 4304, True, False),       # M <= 128 -> 1-CTA kernel, k not a multiple of 64
+])
+def test_gemm_elementwise_error_bound(M, N, K, bias, residual):
+    """Per-ELEMENT bound, much tighter than `close` (which allows ~5 ulps of the LARGEST output on every element, so a
+    dropped k-slab on a small-magnitude row could slip through): against a float64 product of the same bf16 operands the
+    stored value may differ by the final bf16 rounding(s) (1 ulp of the element = 2^-8 |ref|, twice with a residual) plus
+    the fp32 accumulation error, which is bounded by a small multiple of sum_k |a_k w_k| — 2e-4 here, while a lost
+    64-wide k-slab would move an element by ~64/K of that sum (>= 1.5e-2)."""
+    g0 = torch.Generator().manual_seed(3 * M + 5 * N + 7 * K)
+    a = torch.randn(M, K, generator=g0).bfloat16().to(DEV)
+    a[::3] *= 0.01                                           # small-magnitude rows: invisible to a max-scaled tolerance
+    w = (torch.randn(N, K, generator=g0) * 0.05).bfloat16().to(DEV)
+    bs = (torch.randn(N, generator=g0) * 0.02).bfloat16().to(DEV) if bias else None
+    res = (torch.randn(M, N, generator=g0) * 0.05).bfloat16().to(DEV) if residual else None
+    got = ops.gemm_bias_act(a, w, bs, residual=res).double()
+    ref = a.double() @ w.double().t()
+    mag = a.double().abs() @ w.double().abs().t()            # sum_k |a_k w_k|
+    if bias:
+        ref = ref + bs.double()
+        mag = mag + bs.double().abs()
+    lim = 2.0 ** -8 * ref.abs() + 2e-4 * mag
+    if residual:                                             # bf16(bf16(acc + bias) + res): a second rounding
+        lim = lim + 2.0 ** -8 * (ref + res.double()).abs()
+        ref = ref + res.double()
+    err = (got - ref).abs()
+    bad = err > lim
+    assert not bad.any(), f"{int(bad.sum())} of {bad.numel()} elements outside the bound, worst ratio {(err / lim).max().item():.2f}"
+    # the bound does catch a dropped k-slab (the check checks something): zero 64 columns of k and compare again
+    a2 = a.clone()
+    a2[:, 64:128] = 0
+    got2 = ops.gemm_bias_act(a2, w, bs, residual=res).double()
+    assert ((got2 - ref).abs() > lim).float().mean().item() > 0.5
+
+
 def test_gemm_modular_residual_and_strided_output():
     M, N, K, P = 96, 128, 64, 16
     a = torch.randn(M, K, device=DEV).bfloat16()
